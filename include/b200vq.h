@@ -1,0 +1,195 @@
+/*
+ * b200vq.h -- C ABI of the B200-native quantization bottleneck (libb200vq.so).
+ *
+ * Drop-in boundary for the hot path of zhxie0117/video-tokenizer's
+ * models/bottleneck.py.  The reference has no FFI of its own (it is pure PyTorch), so each
+ * entry point cites the reference code it replaces; the Python binding a maintainer adds
+ * (ctypes, no torch types cross this line) is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless it says "host";
+ *   - the library never allocates: scratch comes from a caller workspace
+ *     (b200vq_workspace_bytes), outputs are caller-owned;
+ *   - every call only ENQUEUES work on `stream` (a cudaStream_t); no host sync, no host
+ *     read of device data, CUDA-graph capturable;
+ *   - return value: 0 on success, a negative B200VQ_E* code otherwise
+ *     (b200vq_error_string gives the text);
+ *   - z / grad_z may be fp32, bf16 or fp16 (B200VQ_DT_*); all quantizer arithmetic and all
+ *     other tensors are fp32 (reference bottleneck.py:252,262-264 force fp32), indices are
+ *     int64 (torch.argmin / multinomial dtype).
+ */
+#ifndef B200VQ_H_
+#define B200VQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200VQ_VERSION 100
+
+/* element types of z / grad_z */
+#define B200VQ_DT_F32 0
+#define B200VQ_DT_BF16 1
+#define B200VQ_DT_F16 2
+
+/* code selection rule */
+#define B200VQ_MODE_ARGMIN_DIST 0 /* argmin_k |z|^2+|e_k|^2-2 z.e_k   (bottleneck.py:282-290) */
+#define B200VQ_MODE_ARGMAX_COS 1  /* argmax_k softmax(z.e_k/T) == argmax z.e_k (:277-278)    */
+#define B200VQ_MODE_SAMPLE 2      /* k ~ softmax(z.e_k/T), Gumbel-max       (:275-276,:280)  */
+
+/* error codes */
+#define B200VQ_OK 0
+#define B200VQ_EINVAL (-1)    /* bad shape / size / enum                       */
+#define B200VQ_EDIM (-2)      /* unsupported code dimension D                  */
+#define B200VQ_EALIGN (-3)    /* pointer or stride not aligned as required     */
+#define B200VQ_ECUDA (-4)     /* a CUDA call failed; see b200vq_last_cuda_error */
+#define B200VQ_EWORKSPACE (-5) /* workspace too small / null                    */
+
+typedef void* b200vq_stream_t; /* cudaStream_t */
+
+int b200vq_version(void);
+const char* b200vq_error_string(int code);
+/* cudaError_t of the last failing CUDA call made by this library on this thread */
+int b200vq_last_cuda_error(void);
+/* largest supported code dimension */
+int b200vq_max_dim(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+uint64_t b200vq_launch_count(void);
+
+/* Scratch bytes the forward/backward calls need for N tokens, D dims, K codes. */
+size_t b200vq_workspace_bytes(int64_t N, int D, int64_t K);
+
+/*
+ * get_emb (bottleneck.py:252-259) -- the codebook as the quantizer sees it, once per step.
+ *   weight (K,D) fp32 raw embedding.weight
+ *   emb    (K,D) fp32 out: weight / max(|weight|,1e-12) if l2norm else a copy
+ *   e2     (K)   fp32 out: sum_d emb^2   (the |e_k|^2 term of :283-285)
+ *   wnorm  (K)   fp32 out: |weight_k| (unclamped; the backward's normalise Jacobian needs it)
+ */
+int b200vq_prepare_codebook(const float* weight, int64_t K, int D, int l2norm,
+                            float* emb, float* e2, float* wnorm, b200vq_stream_t stream);
+
+/*
+ * Selection keys.  key[i] = (orderable(score_i,best) << 32) | ~k_best ; unsigned max over
+ * keys == best score, lowest index on ties.  keys must be reset before the first partial
+ * call of a step.
+ */
+int b200vq_keys_reset(uint64_t* keys, int64_t N, b200vq_stream_t stream);
+
+/*
+ * Scoring pass over a slice [k_offset, k_offset+K_local) of the codebook
+ * (bottleneck.py:264-290 without materialising the N x K matrix).  Normalises z rows on
+ * the fly, streams the slice through shared memory, keeps a per-row running best and
+ * merges it into keys[] with a 64-bit atomic max.  Token-sharded / single GPU: one call
+ * with the whole codebook.  Codebook-sharded: one call per rank on its slice, then an
+ * all-reduce(MAX, uint64) of keys[].
+ *   z         (N,D) rows, element type z_dtype, row stride z_row_stride ELEMENTS
+ *   emb, e2   slice base pointers (already offset by the caller: emb + k_offset*D)
+ *   t_inv     1/T (MODE_SAMPLE only)
+ *   seed, offset  Philox key / stream offset (MODE_SAMPLE only), taken from the torch CUDA
+ *             generator by the host wrapper; noise is keyed by (row_offset+i, k_offset+k)
+ *             so draws do not depend on tiling or sharding
+ */
+int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
+                          const float* emb, const float* e2, int64_t K_local, int64_t k_offset,
+                          int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                          int64_t row_offset, uint64_t* keys, b200vq_stream_t stream);
+
+/*
+ * Gather + straight-through + losses + usage histograms from keys
+ * (bottleneck.py:292-298, :304-310; trainer bincounts larp_tokenizer_trainer.py:337-343).
+ *   emb        full (K,D) normalised codebook (may be null when q_rows is given)
+ *   q_rows     nullable (N,D): the selected code rows already gathered (codebook-sharded
+ *              mode, where no rank holds the whole codebook); else rows come from emb
+ *   n_first    number of leading rows that belong to sample 0 of the batch (token_nums);
+ *              those also count into hist_first (the trainer's "first instance" stats)
+ *   znorm_out  (N,D) fp32  'unregularized_z'  (normalised z)
+ *   ste_out    (N,D) fp32  'regularized_z'    z + (q - z)
+ *   idx_out    (N)   int64 'bottleneck_rep'
+ *   zlen_out   (N)   fp32  |z_i| (unclamped) for the backward
+ *   hist, hist_first (K) int32, ACCUMULATED into (caller zeroes them)
+ *   sqerr      (1) double, ACCUMULATED: sum_i |q_i - z_i|^2 (caller zeroes)
+ *   losses     (3) fp32 out when finalize!=0: loss_q, loss_commit, loss_codebook computed
+ *              from sqerr / (N_total*D) with beta, w_cb  (:295-298,:304)
+ */
+int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
+                  const float* emb, int64_t K, const uint64_t* keys, const float* q_rows, int l2norm,
+                  int64_t n_first,
+                  float* znorm_out, float* ste_out, int64_t* idx_out, float* zlen_out,
+                  int32_t* hist, int32_t* hist_first, double* sqerr,
+                  int finalize, int64_t N_total, float beta, float w_cb, float* losses,
+                  b200vq_stream_t stream);
+
+/*
+ * One-call forward for the unsharded case: keys_reset + scores_partial(whole codebook) +
+ * finish(finalize=1).  workspace >= b200vq_workspace_bytes(N,D,K); hist/hist_first/sqerr
+ * are zeroed inside.
+ */
+int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
+                   const float* emb, const float* e2, int64_t K,
+                   int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                   int64_t n_first, float beta, float w_cb,
+                   float* znorm_out, float* ste_out, int64_t* idx_out, float* zlen_out,
+                   int32_t* hist, int32_t* hist_first, float* losses,
+                   void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
+
+/*
+ * Fused backward of SimpleVectorQuantizer.forward (autograd of bottleneck.py:292-307;
+ * closed form in SURVEY.md 8a-5): straight-through + commitment gradient pushed through
+ * the normalise Jacobian into grad_z, and the codebook-loss gradient scatter-added into
+ * grad_emb (K,D) (zeroed inside).
+ *   g_ste      (N,D) fp32 grad of 'regularized_z'      (nullable = 0)
+ *   g_znorm    (N,D) fp32 grad of 'unregularized_z'    (nullable = 0)
+ *   g_loss     (3)   fp32 DEVICE grads of loss_q, loss_commit, loss_codebook (nullable = 0)
+ *   znorm      (N,D) fp32 saved normalised z ; zlen (N) saved |z|
+ *   idx        (N)   int64 saved (global) indices
+ *   emb        (K,D) the codebook rows [k_offset, k_offset+K) this rank owns (K = full
+ *              codebook and k_offset = 0 when unsharded); grad_emb covers the same rows and
+ *              only owned codes are scatter-added
+ *   q_rows     nullable (N,D) selected code rows (required when the codebook is sharded)
+ *   grad_z     (N,D) out, element type gz_dtype, contiguous
+ *   grad_emb   (K,D) fp32 out: d loss / d emb  (before the codebook normalise Jacobian)
+ */
+int b200vq_backward(const float* g_ste, const float* g_znorm, const float* g_loss,
+                    const float* znorm, const float* zlen, const int64_t* idx, const float* emb,
+                    const float* q_rows, int64_t k_offset,
+                    int64_t N, int D, int64_t K, int l2norm, int64_t N_total, float beta, float w_cb,
+                    void* grad_z, int gz_dtype, float* grad_emb, b200vq_stream_t stream);
+
+/*
+ * Codebook side of the backward: grad_weight = J_normalise(weight)^T (grad_emb + g_emb)
+ * (autograd of F.normalize at bottleneck.py:255).  g_emb = upstream grad on 'emb', nullable.
+ */
+int b200vq_codebook_backward(const float* grad_emb, const float* g_emb, const float* emb,
+                             const float* wnorm, int64_t K, int D, int l2norm, float* grad_weight,
+                             b200vq_stream_t stream);
+
+/*
+ * get_codebook_entry / decode (bottleneck.py:327-344): out[i] = normalise(weight[idx[i]]).
+ * Out-of-range indices make the call write NaN rows and set *bad_flag (device int, nullable).
+ */
+int b200vq_decode(const int64_t* idx, int64_t n, const float* weight, int64_t K, int D, int l2norm,
+                  float* out, int* bad_flag, b200vq_stream_t stream);
+
+/*
+ * Trainer code-usage statistics from the fused histograms
+ * (larp_tokenizer_trainer.py:335-352, utils/statistics.py:5-32), on device:
+ *   out[0]=index_usage  out[1]=index_usage_batch  out[2]=kl_uni  out[3]=perplexity
+ */
+int b200vq_usage_stats(const int32_t* hist_first, const int32_t* hist_batch, int64_t K,
+                       float* out4, b200vq_stream_t stream);
+
+/*
+ * Codebook-sharded helper: out[i] = emb_local[idx_i - k_offset] if this rank owns idx_i else 0
+ * (rows are then summed across ranks).  keys are the all-reduced keys.
+ */
+int b200vq_gather_owned(const uint64_t* keys, int64_t N, const float* emb_local, int64_t K_local,
+                        int64_t k_offset, int D, float* out, b200vq_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VQ_H_ */

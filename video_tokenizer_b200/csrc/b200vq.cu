@@ -1,0 +1,287 @@
+// b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
+#include "vq_generic.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+
+using namespace b200vq;
+
+namespace {
+
+thread_local int g_last_cuda_error = 0;
+
+inline int cuda_check(cudaError_t e) {
+    if (e == cudaSuccess) return B200VQ_OK;
+    g_last_cuda_error = static_cast<int>(e);
+    cudaGetLastError();  // clear the sticky launch error so later calls can proceed
+    return B200VQ_ECUDA;
+}
+std::atomic<unsigned long long> g_launches{0};
+inline int launch_check() { g_launches.fetch_add(1, std::memory_order_relaxed); return cuda_check(cudaPeekAtLastError()); }
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+inline bool valid_dtype(int dt) { return dt == B200VQ_DT_F32 || dt == B200VQ_DT_BF16 || dt == B200VQ_DT_F16; }
+inline bool valid_mode(int m) { return m >= B200VQ_MODE_ARGMIN_DIST && m <= B200VQ_MODE_SAMPLE; }
+inline bool specialised_dim(int D) { return D == 8 || D == 16 || D == 24 || D == 32 || D == 64; }
+
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
+
+// ---- dispatch helpers -------------------------------------------------------------------
+#define B200VQ_DISPATCH_DTYPE(dt, T, ...)                                              \
+    switch (dt) {                                                                      \
+        case B200VQ_DT_F32: { using T = float; __VA_ARGS__; break; }                   \
+        case B200VQ_DT_BF16: { using T = __nv_bfloat16; __VA_ARGS__; break; }          \
+        default: { using T = __half; __VA_ARGS__; break; }                             \
+    }
+#define B200VQ_DISPATCH_DIM(D, DD, ...)                                                \
+    switch (D) {                                                                       \
+        case 8: { constexpr int DD = 8; __VA_ARGS__; break; }                          \
+        case 16: { constexpr int DD = 16; __VA_ARGS__; break; }                        \
+        case 24: { constexpr int DD = 24; __VA_ARGS__; break; }                        \
+        case 32: { constexpr int DD = 32; __VA_ARGS__; break; }                        \
+        default: { constexpr int DD = 64; __VA_ARGS__; break; }                        \
+    }
+#define B200VQ_DISPATCH_MODE(m, MM, ...)                                               \
+    switch (m) {                                                                       \
+        case B200VQ_MODE_ARGMIN_DIST: { constexpr int MM = B200VQ_MODE_ARGMIN_DIST; __VA_ARGS__; break; } \
+        case B200VQ_MODE_ARGMAX_COS: { constexpr int MM = B200VQ_MODE_ARGMAX_COS; __VA_ARGS__; break; }   \
+        default: { constexpr int MM = B200VQ_MODE_SAMPLE; __VA_ARGS__; break; }        \
+    }
+
+}  // namespace
+
+extern "C" {
+
+int b200vq_version(void) { return B200VQ_VERSION; }
+int b200vq_last_cuda_error(void) { return g_last_cuda_error; }
+int b200vq_max_dim(void) { return kMaxDim; }
+uint64_t b200vq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+const char* b200vq_error_string(int code) {
+    switch (code) {
+        case B200VQ_OK: return "ok";
+        case B200VQ_EINVAL: return "invalid argument (shape, size or enum)";
+        case B200VQ_EDIM: return "unsupported code dimension";
+        case B200VQ_EALIGN: return "pointer or offset not aligned as required";
+        case B200VQ_ECUDA: return "CUDA error (see b200vq_last_cuda_error)";
+        case B200VQ_EWORKSPACE: return "workspace null or too small";
+        default: return "unknown error";
+    }
+}
+
+size_t b200vq_workspace_bytes(int64_t N, int D, int64_t K) {
+    (void)D; (void)K;
+    if (N < 0) return 0;
+    // [keys: N u64][scratch: sum + ticket, 2 doubles]
+    return align_up(static_cast<size_t>(N) * sizeof(uint64_t)) + align_up(2 * sizeof(double));
+}
+
+int b200vq_prepare_codebook(const float* weight, int64_t K, int D, int l2norm, float* emb, float* e2,
+                            float* wnorm, b200vq_stream_t stream) {
+    if (!weight || !emb || !e2 || !wnorm || K <= 0 || D <= 0 || D > kMaxDim) return B200VQ_EINVAL;
+    const int64_t threads = K * 32;
+    const unsigned blocks = static_cast<unsigned>((threads + 255) / 256);
+    prepare_codebook_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, K, D, l2norm, emb, e2, wnorm);
+    return launch_check();
+}
+
+int b200vq_keys_reset(uint64_t* keys, int64_t N, b200vq_stream_t stream) {
+    if (N < 0 || (N > 0 && !keys)) return B200VQ_EINVAL;
+    if (N == 0) return B200VQ_OK;
+    return cuda_check(cudaMemsetAsync(keys, 0, static_cast<size_t>(N) * sizeof(uint64_t), static_cast<cudaStream_t>(stream)));
+}
+
+int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb,
+                          const float* e2, int64_t K_local, int64_t k_offset, int mode, int l2norm, float t_inv,
+                          uint64_t seed, uint64_t offset, int64_t row_offset, uint64_t* keys,
+                          b200vq_stream_t stream) {
+    if (N < 0 || K_local < 0 || k_offset < 0 || row_offset < 0 || !valid_dtype(z_dtype) || !valid_mode(mode))
+        return B200VQ_EINVAL;
+    if (D <= 0 || D > kMaxDim) return B200VQ_EDIM;
+    if (N == 0 || K_local == 0) return B200VQ_OK;
+    if (!z || !emb || !e2 || !keys || z_row_stride < D) return B200VQ_EINVAL;
+    if (k_offset + K_local > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
+    if (mode == B200VQ_MODE_SAMPLE && (k_offset & 3)) return B200VQ_EALIGN;  // Philox groups of 4 codes
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
+    if (specialised_dim(D)) {
+        const int64_t row_tiles = (N + 127) / 128;
+        B200VQ_DISPATCH_DIM(D, DD, {
+            constexpr int TK = TileCodes<DD>::value;
+            // enough CTAs for >= 4 waves-worth of residency when the token count is small
+            const int64_t want = 4ll * sm_count();
+            int64_t splits = std::max<int64_t>(1, (want + row_tiles - 1) / row_tiles);
+            const int64_t max_splits = (K_local + TK - 1) / TK;
+            splits = std::min(splits, max_splits);
+            int64_t per = (K_local + splits - 1) / splits;
+            per = (per + TK - 1) / TK * TK;
+            splits = (K_local + per - 1) / per;
+            dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+            B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+                B200VQ_DISPATCH_MODE(mode, MM, {
+                    scores_kernel<DD, T, MM><<<grid, 128, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, emb, e2,
+                                                                    K_local, k_offset, per, l2norm, t_inv, seed,
+                                                                    offset, row_offset, k64);
+                });
+            });
+        });
+    } else {
+        const int64_t row_tiles = (N + 63) / 64;
+        const int64_t want = 8ll * sm_count();
+        int64_t splits = std::max<int64_t>(1, (want + row_tiles - 1) / row_tiles);
+        splits = std::min<int64_t>(splits, (K_local + 63) / 64);
+        int64_t per = (K_local + splits - 1) / splits;
+        per = (per + 3) / 4 * 4;
+        splits = (K_local + per - 1) / per;
+        dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+        const size_t smem = static_cast<size_t>(64) * (D + 1) * sizeof(float);
+        B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+            B200VQ_DISPATCH_MODE(mode, MM, {
+                if (smem > 48 * 1024)
+                    cudaFuncSetAttribute(scores_generic_kernel<T, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+                scores_generic_kernel<T, MM><<<grid, 64, smem, st>>>(static_cast<const T*>(z), z_row_stride, N, D, emb,
+                                                                     e2, K_local, k_offset, per, l2norm, t_inv, seed,
+                                                                     offset, row_offset, k64);
+            });
+        });
+    }
+    return launch_check();
+}
+
+int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb, int64_t K,
+                  const uint64_t* keys, const float* q_rows, int l2norm, int64_t n_first, float* znorm_out, float* ste_out,
+                  int64_t* idx_out, float* zlen_out, int32_t* hist, int32_t* hist_first, double* sqerr, int finalize,
+                  int64_t N_total, float beta, float w_cb, float* losses, b200vq_stream_t stream) {
+    if (N < 0 || K <= 0 || !valid_dtype(z_dtype)) return B200VQ_EINVAL;
+    if (D <= 0 || D > kMaxDim) return B200VQ_EDIM;
+    if (N == 0) return B200VQ_OK;
+    if (!z || (!emb && !q_rows) || !keys || !znorm_out || !ste_out || !idx_out || !zlen_out || !sqerr || z_row_stride < D)
+        return B200VQ_EINVAL;
+    if (finalize && (!losses || N_total <= 0)) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned blocks = static_cast<unsigned>((N + 127) / 128);
+    const unsigned long long* k64 = reinterpret_cast<const unsigned long long*>(keys);
+    if (specialised_dim(D)) {
+        B200VQ_DISPATCH_DIM(D, DD, {
+            B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+                finish_kernel<DD, T><<<blocks, 128, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, emb, K, k64,
+                                                             q_rows, l2norm, n_first, znorm_out, ste_out, idx_out, zlen_out,
+                                                             hist, hist_first, sqerr, finalize, N_total, beta, w_cb,
+                                                             losses);
+            });
+        });
+    } else {
+        B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+            finish_generic_kernel<T><<<blocks, 128, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, D, emb, K, k64,
+                                                             q_rows, l2norm, n_first, znorm_out, ste_out, idx_out, zlen_out,
+                                                             hist, hist_first, sqerr, finalize, N_total, beta, w_cb,
+                                                             losses);
+        });
+    }
+    return launch_check();
+}
+
+int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb,
+                   const float* e2, int64_t K, int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                   int64_t n_first, float beta, float w_cb, float* znorm_out, float* ste_out, int64_t* idx_out,
+                   float* zlen_out, int32_t* hist, int32_t* hist_first, float* losses, void* workspace,
+                   size_t workspace_bytes, b200vq_stream_t stream) {
+    if (N <= 0 || K <= 0) return B200VQ_EINVAL;
+    if (!workspace || workspace_bytes < b200vq_workspace_bytes(N, D, K)) return B200VQ_EWORKSPACE;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint64_t* keys = static_cast<uint64_t*>(workspace);
+    double* scratch = reinterpret_cast<double*>(static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8));
+    int rc = cuda_check(cudaMemsetAsync(workspace, 0, b200vq_workspace_bytes(N, D, K), st));
+    if (rc) return rc;
+    if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
+    if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
+    rc = b200vq_scores_partial(z, z_dtype, z_row_stride, N, D, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
+                               keys, stream);
+    if (rc) return rc;
+    return b200vq_finish(z, z_dtype, z_row_stride, N, D, emb, K, keys, nullptr, l2norm, n_first, znorm_out, ste_out, idx_out,
+                         zlen_out, hist, hist_first, scratch, 1, N, beta, w_cb, losses, stream);
+}
+
+int b200vq_backward(const float* g_ste, const float* g_znorm, const float* g_loss, const float* znorm,
+                    const float* zlen, const int64_t* idx, const float* emb, const float* q_rows,
+                    int64_t k_offset, int64_t N, int D, int64_t K, int l2norm, int64_t N_total, float beta, float w_cb, void* grad_z, int gz_dtype, float* grad_emb,
+                    b200vq_stream_t stream) {
+    if (N < 0 || K <= 0 || N_total <= 0 || !valid_dtype(gz_dtype)) return B200VQ_EINVAL;
+    if (D <= 0 || D > kMaxDim) return B200VQ_EDIM;
+    if (!grad_emb) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = cuda_check(cudaMemsetAsync(grad_emb, 0, static_cast<size_t>(K) * D * sizeof(float), st));
+    if (rc) return rc;
+    if (N == 0) return B200VQ_OK;
+    if (!znorm || !zlen || !idx || (!emb && !q_rows) || !grad_z || k_offset < 0) return B200VQ_EINVAL;
+    const unsigned blocks = static_cast<unsigned>((N + 127) / 128);
+    if (specialised_dim(D)) {
+        B200VQ_DISPATCH_DIM(D, DD, {
+            B200VQ_DISPATCH_DTYPE(gz_dtype, T, {
+                backward_kernel<DD, T><<<blocks, 128, 0, st>>>(g_ste, g_znorm, g_loss, znorm, zlen, idx, emb, q_rows, k_offset, K, N, l2norm,
+                                                               N_total, beta, w_cb, static_cast<T*>(grad_z), grad_emb);
+            });
+        });
+    } else {
+        B200VQ_DISPATCH_DTYPE(gz_dtype, T, {
+            backward_generic_kernel<T><<<blocks, 128, 0, st>>>(g_ste, g_znorm, g_loss, znorm, zlen, idx, emb, q_rows, k_offset, K, N, D,
+                                                               l2norm, N_total, beta, w_cb, static_cast<T*>(grad_z),
+                                                               grad_emb);
+        });
+    }
+    return launch_check();
+}
+
+int b200vq_codebook_backward(const float* grad_emb, const float* g_emb, const float* emb, const float* wnorm,
+                             int64_t K, int D, int l2norm, float* grad_weight, b200vq_stream_t stream) {
+    if (!grad_emb || !emb || !wnorm || !grad_weight || K <= 0 || D <= 0 || D > kMaxDim) return B200VQ_EINVAL;
+    const unsigned blocks = static_cast<unsigned>((K * 32 + 255) / 256);
+    codebook_backward_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad_emb, g_emb, emb, wnorm, K, D,
+                                                                                   l2norm, grad_weight);
+    return launch_check();
+}
+
+int b200vq_decode(const int64_t* idx, int64_t n, const float* weight, int64_t K, int D, int l2norm, float* out,
+                  int* bad_flag, b200vq_stream_t stream) {
+    if (n < 0 || K <= 0 || D <= 0 || D > kMaxDim) return B200VQ_EINVAL;
+    if (n == 0) return B200VQ_OK;
+    if (!idx || !weight || !out) return B200VQ_EINVAL;
+    const unsigned blocks = static_cast<unsigned>((n * 32 + 255) / 256);
+    decode_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(idx, n, weight, K, D, l2norm, out, bad_flag);
+    return launch_check();
+}
+
+int b200vq_usage_stats(const int32_t* hist_first, const int32_t* hist_batch, int64_t K, float* out4,
+                       b200vq_stream_t stream) {
+    if (!hist_first || !hist_batch || !out4 || K <= 0) return B200VQ_EINVAL;
+    usage_stats_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(hist_first, hist_batch, K, out4);
+    return launch_check();
+}
+
+int b200vq_gather_owned(const uint64_t* keys, int64_t N, const float* emb_local, int64_t K_local, int64_t k_offset,
+                        int D, float* out, b200vq_stream_t stream) {
+    if (N < 0 || K_local < 0 || D <= 0) return B200VQ_EINVAL;
+    if (N == 0) return B200VQ_OK;
+    if (!keys || !out || (K_local > 0 && !emb_local)) return B200VQ_EINVAL;
+    const int64_t total = N * D;
+    gather_owned_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const unsigned long long*>(keys), N, emb_local, K_local, k_offset, D, out);
+    return launch_check();
+}
+
+}  // extern "C"

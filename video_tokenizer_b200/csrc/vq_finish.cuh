@@ -1,0 +1,229 @@
+// b200vq -- gather / straight-through / loss / histogram, backward, decode, statistics.
+#pragma once
+#include "vq_scores.cuh"
+
+namespace b200vq {
+
+// =======================================================================================
+// Finish: keys -> indices, gather, STE output, squared-error sum, usage histograms.
+// (bottleneck.py:292-298, :304-310; trainer bincounts larp_tokenizer_trainer.py:337-343)
+// One thread per row; block = 128.  scratch[0] = double sum, scratch[1] = block ticket.
+// =======================================================================================
+template <int D, typename T>
+__global__ void __launch_bounds__(128) finish_kernel(const T* __restrict__ z, int64_t z_row_stride, int64_t N,
+                                                     const float* __restrict__ emb, int64_t K,
+                                                     const unsigned long long* __restrict__ keys,
+        const float* __restrict__ q_rows, int l2norm,
+                                                     int64_t n_first, float* __restrict__ znorm_out,
+                                                     float* __restrict__ ste_out, int64_t* __restrict__ idx_out,
+                                                     float* __restrict__ zlen_out, int32_t* __restrict__ hist,
+                                                     int32_t* __restrict__ hist_first, double* __restrict__ scratch,
+                                                     int finalize, int64_t N_total, float beta, float w_cb,
+                                                     float* __restrict__ losses) {
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * 128 + threadIdx.x;
+    float sq = 0.f;
+    if (row < N) {
+        float zn[D];
+        float z2, zlen;
+        load_normalised_row<D, T>(z + row * z_row_stride, l2norm, zn, z2, zlen);
+        uint32_t code = key_code(keys[row]);
+        if (code >= K) code = 0;  // unreachable for valid keys; keeps the gather in bounds
+        const float* q = q_rows ? q_rows + row * D : emb + static_cast<int64_t>(code) * D;
+        float* zo = znorm_out + row * D;
+        float* so = ste_out + row * D;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const float qd = __ldg(q + d);
+            const float diff = __fsub_rn(qd, zn[d]);
+            zo[d] = zn[d];
+            so[d] = __fadd_rn(zn[d], diff);  // z + (q - z).detach()   (:307)
+            sq = fmaf(diff, diff, sq);
+        }
+        idx_out[row] = static_cast<int64_t>(code);
+        zlen_out[row] = zlen;
+        if (hist) atomicAdd(hist + code, 1);
+        if (hist_first && row < n_first) atomicAdd(hist_first + code, 1);
+    }
+    // block reduction of the squared error, one double atomic per block
+    __shared__ float s_part[4];
+    sq = warp_sum(sq);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = sq;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double tot = static_cast<double>(s_part[0]) + s_part[1] + s_part[2] + s_part[3];
+        atomicAdd(scratch, tot);
+        if (finalize) {
+            __threadfence();
+            unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 1);
+            const unsigned int t = atomicAdd(ticket, 1u);
+            if (t == gridDim.x - 1) {
+                __threadfence();
+                const double s = *reinterpret_cast<volatile double*>(scratch);
+                const float l = static_cast<float>(s / (static_cast<double>(N_total) * D));
+                losses[1] = l;                                        // loss_commit   (:295,:297)
+                losses[2] = l;                                        // loss_codebook (:296,:298)
+                losses[0] = __fadd_rn(__fmul_rn(beta, l), __fmul_rn(w_cb, l));  // loss_q (:304), entropy weight 0
+            }
+        }
+    }
+}
+
+// =======================================================================================
+// Backward.  One thread per row.  coef from device scalars so no host sync is needed.
+// =======================================================================================
+template <int D, typename GT>
+__global__ void __launch_bounds__(128) backward_kernel(const float* __restrict__ g_ste, const float* __restrict__ g_zn,
+                                                       const float* __restrict__ g_loss,
+                                                       const float* __restrict__ znorm, const float* __restrict__ zlen,
+                                                       const int64_t* __restrict__ idx, const float* __restrict__ emb,
+                                                       const float* __restrict__ q_rows, int64_t k_offset, int64_t K_local,
+                                                       int64_t N, int l2norm, int64_t N_total, float beta, float w_cb,
+                                                       GT* __restrict__ grad_z, float* __restrict__ grad_emb) {
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * 128 + threadIdx.x;
+    if (row >= N) return;
+    float gq = 0.f, gc = 0.f, gb = 0.f;
+    if (g_loss) { gq = __ldg(g_loss); gc = __ldg(g_loss + 1); gb = __ldg(g_loss + 2); }
+    const float c = 2.0f / (static_cast<float>(N_total) * D);
+    const float a = (gq * beta + gc) * c;   // commitment: d/dz  of mean((q.detach()-z)^2)
+    const float b = (gq * w_cb + gb) * c;   // codebook:   d/dq  of mean((q-z.detach())^2)
+    const int64_t code = idx[row] - k_offset;
+    const bool owned = code >= 0 && code < K_local;
+    const float* q = q_rows ? q_rows + row * D : emb + (owned ? code : 0) * D;
+    float zn[D], dzh[D];
+    float proj = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        zn[d] = znorm[row * D + d];
+        const float qd = __ldg(q + d);
+        float g = a * (zn[d] - qd);
+        if (g_ste) g += g_ste[row * D + d];
+        if (g_zn) g += g_zn[row * D + d];
+        dzh[d] = g;
+        proj = fmaf(zn[d], g, proj);
+        if (b != 0.f && owned) atomicAdd(grad_emb + code * D + d, b * (qd - zn[d]));
+    }
+    GT* out = grad_z + row * D;
+    if (l2norm) {
+        const float len = zlen[row];
+        if (len > kNormEps) {
+            const float inv = 1.0f / len;
+#pragma unroll
+            for (int d = 0; d < D; ++d) out[d] = from_f32<GT>((dzh[d] - zn[d] * proj) * inv);
+        } else {
+#pragma unroll
+            for (int d = 0; d < D; ++d) out[d] = from_f32<GT>(dzh[d] * (1.0f / kNormEps));
+        }
+    } else {
+#pragma unroll
+        for (int d = 0; d < D; ++d) out[d] = from_f32<GT>(dzh[d]);
+    }
+}
+
+// grad_weight = J_normalise^T (grad_emb + g_emb).  One warp per code row.
+__global__ void __launch_bounds__(256) codebook_backward_kernel(const float* __restrict__ grad_emb,
+                                                                const float* __restrict__ g_emb,
+                                                                const float* __restrict__ emb,
+                                                                const float* __restrict__ wnorm, int64_t K, int D,
+                                                                int l2norm, float* __restrict__ grad_weight) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (row >= K) return;
+    float proj = 0.f;
+    for (int d = lane; d < D; d += 32) {
+        float g = grad_emb[row * D + d];
+        if (g_emb) g += g_emb[row * D + d];
+        proj = fmaf(emb[row * D + d], g, proj);
+    }
+    proj = warp_sum(proj);
+    const float wn = wnorm[row];
+    for (int d = lane; d < D; d += 32) {
+        float g = grad_emb[row * D + d];
+        if (g_emb) g += g_emb[row * D + d];
+        float o = g;
+        if (l2norm) o = wn > kNormEps ? (g - emb[row * D + d] * proj) / wn : g * (1.0f / kNormEps);
+        grad_weight[row * D + d] = o;
+    }
+}
+
+// get_codebook_entry (bottleneck.py:327-341).  One warp per index.
+__global__ void __launch_bounds__(256) decode_kernel(const int64_t* __restrict__ idx, int64_t n,
+                                                     const float* __restrict__ w, int64_t K, int D, int l2norm,
+                                                     float* __restrict__ out, int* __restrict__ bad_flag) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (i >= n) return;
+    const int64_t code = idx[i];
+    if (code < 0 || code >= K) {
+        for (int d = lane; d < D; d += 32) out[i * D + d] = __int_as_float(0x7fc00000);
+        if (bad_flag && lane == 0) atomicExch(bad_flag, 1);
+        return;
+    }
+    const float* wr = w + code * D;
+    float ss = 0.f;
+    for (int d = lane; d < D; d += 32) { const float v = __ldg(wr + d); ss = fmaf(v, v, ss); }
+    ss = warp_sum(ss);
+    const float den = l2norm ? fmaxf(sqrtf(ss), kNormEps) : 1.0f;
+    for (int d = lane; d < D; d += 32) out[i * D + d] = l2norm ? __fdiv_rn(__ldg(wr + d), den) : __ldg(wr + d);
+}
+
+// Trainer usage statistics (larp_tokenizer_trainer.py:335-352).  Single block of 1024.
+__global__ void __launch_bounds__(1024) usage_stats_kernel(const int32_t* __restrict__ hf, const int32_t* __restrict__ hb,
+                                                           int64_t K, float* __restrict__ out4) {
+    __shared__ double s_red[32];
+    __shared__ double s_bcast;
+    auto block_sum = [&](double v) -> double {
+        v = warp_sum_d(v);
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            double t = s_red[threadIdx.x];
+            t = warp_sum_d(t);
+            if (threadIdx.x == 0) s_bcast = t;
+        }
+        __syncthreads();
+        return s_bcast;
+    };
+    double nzf = 0, nzb = 0, tot = 0;
+    for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
+        const int cf = hf[k], cb = hb[k];
+        nzf += cf > 0; nzb += cb > 0; tot += cf;
+    }
+    nzf = block_sum(nzf); nzb = block_sum(nzb); tot = block_sum(tot);
+    double kl = 0, ent = 0;
+    if (tot > 0) {
+        const double logK = log(static_cast<double>(K));
+        for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
+            const int cf = hf[k];
+            // avg_probs = one_hot.float().mean(0) -> fp32 count/n ; log(avg + 1e-10) in fp32
+            const float avg = static_cast<float>(cf) / static_cast<float>(tot);
+            ent -= static_cast<double>(avg * logf(avg + 1e-10f));
+            if (cf > 0) { const double p = cf / tot; kl += p * (log(p) + logK); }
+        }
+    }
+    kl = block_sum(kl); ent = block_sum(ent);
+    if (threadIdx.x == 0) {
+        out4[0] = static_cast<float>(nzf / static_cast<double>(K));
+        out4[1] = static_cast<float>(nzb / static_cast<double>(K));
+        out4[2] = static_cast<float>(kl);
+        out4[3] = static_cast<float>(exp(ent));
+    }
+}
+
+__global__ void __launch_bounds__(256) gather_owned_kernel(const unsigned long long* __restrict__ keys, int64_t N,
+                                                           const float* __restrict__ emb_local, int64_t K_local,
+                                                           int64_t k_offset, int D, float* __restrict__ out) {
+    const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= N * D) return;
+    const int64_t row = t / D;
+    const int d = static_cast<int>(t - row * D);
+    const int64_t code = static_cast<int64_t>(key_code(keys[row])) - k_offset;
+    out[t] = (code >= 0 && code < K_local) ? emb_local[code * D + d] : 0.f;
+}
+
+__global__ void keys_reset_kernel(unsigned long long* keys, int64_t N) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < N) keys[i] = 0ull;
+}
+
+}  // namespace b200vq

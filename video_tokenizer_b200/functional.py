@@ -1,0 +1,186 @@
+"""Autograd-level wrappers over the C ABI (include/b200vq.h).
+
+Torch is plumbing here: it owns device memory, streams and the autograd tape; every
+numeric step of the quantizer runs in libb200vq.so.  There is no CPU path: tensors that
+are not on a CUDA device raise.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_DTYPES = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16, torch.float16: _lib.DT_F16}
+_workspaces: dict = {}
+
+
+def _require_cuda(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(f"video_tokenizer_b200: '{name}' must be a CUDA tensor (the B200 path has no CPU fallback)")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def rows_view(z: torch.Tensor) -> Tuple[torch.Tensor, int]:
+    """(tensor, row stride in elements) such that row i of the flattened (N, D) view starts
+    at data_ptr + i*stride.  Copies only when the layout is not row-uniform."""
+    D = z.shape[-1]
+    if z.dim() == 2:
+        if z.stride(1) == 1 and z.stride(0) >= D:
+            return z, z.stride(0)
+    elif z.dim() == 3:
+        B, n, _ = z.shape
+        if z.stride(2) == 1 and z.stride(1) >= D and (B == 1 or z.stride(0) == n * z.stride(1)):
+            return z, z.stride(1)
+    zc = z.contiguous()
+    return zc, D
+
+
+def philox_state(device: torch.device) -> Tuple[int, int]:
+    """(seed, offset) from the torch CUDA generator, advancing it, so checkpointed RNG
+    state reproduces the stochastic draws (reference consumes the same generator through
+    torch.multinomial, bottleneck.py:280)."""
+    gen = torch.cuda.default_generators[device.index if device.index is not None else torch.cuda.current_device()]
+    seed = gen.initial_seed() & 0xFFFFFFFFFFFFFFFF
+    offset = gen.get_offset()
+    gen.set_offset(offset + 4)
+    return seed, offset
+
+
+def prepare_codebook(weight: torch.Tensor, l2norm: bool):
+    """-> emb (K,D), e2 (K), wnorm (K)  [get_emb, bottleneck.py:252-259]"""
+    _require_cuda(weight, "embedding.weight")
+    assert weight.dtype == torch.float32, f"Embedding weight dtype is {weight.dtype}, expected float32"
+    w = weight.detach().contiguous()
+    K, D = w.shape
+    emb = torch.empty_like(w)
+    e2 = torch.empty(K, dtype=torch.float32, device=w.device)
+    wnorm = torch.empty(K, dtype=torch.float32, device=w.device)
+    lib = _lib.load()
+    with torch.cuda.device(w.device):
+        _lib.check(lib.b200vq_prepare_codebook(w.data_ptr(), K, D, int(l2norm), emb.data_ptr(), e2.data_ptr(),
+                                               wnorm.data_ptr(), _stream()), "b200vq_prepare_codebook")
+    return emb, e2, wnorm
+
+
+class _VQFunction(torch.autograd.Function):
+    """forward = b200vq_prepare_codebook + b200vq_forward; backward = b200vq_backward +
+    b200vq_codebook_backward.  Outputs: znorm, emb, ste, idx, losses(3), hist, hist_first."""
+
+    @staticmethod
+    def forward(ctx, z, weight, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset):
+        _require_cuda(z, "z")
+        _require_cuda(weight, "embedding.weight")
+        if z.dtype not in _DTYPES:
+            raise ValueError(f"unsupported latent dtype {z.dtype}")
+        lib = _lib.load()
+        dev = z.device
+        D = z.shape[-1]
+        K = weight.shape[0]
+        if weight.shape[1] != D:
+            raise ValueError(f"latent dim {D} != codebook dim {weight.shape[1]}")
+        zz, stride = rows_view(z.detach())
+        N = zz.shape[:-1].numel()
+        with torch.cuda.device(dev):
+            emb, e2, wnorm = prepare_codebook(weight, l2norm)
+            znorm = torch.empty(*z.shape, dtype=torch.float32, device=dev)
+            ste = torch.empty(*z.shape, dtype=torch.float32, device=dev)
+            idx = torch.empty(N, dtype=torch.int64, device=dev)
+            zlen = torch.empty(N, dtype=torch.float32, device=dev)
+            hist = torch.empty(K, dtype=torch.int32, device=dev)
+            hist_first = torch.empty(K, dtype=torch.int32, device=dev)
+            losses = torch.empty(3, dtype=torch.float32, device=dev)
+            nbytes = lib.b200vq_workspace_bytes(N, D, K)
+            ws = _workspace(dev, nbytes)
+            rc = lib.b200vq_forward(zz.data_ptr(), _DTYPES[zz.dtype], stride, N, D, emb.data_ptr(), e2.data_ptr(), K,
+                                    mode, int(l2norm), float(t_inv), seed, offset, int(n_first), float(beta),
+                                    float(w_cb), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(),
+                                    hist.data_ptr(), hist_first.data_ptr(), losses.data_ptr(), ws.data_ptr(),
+                                    ws.numel(), _stream())
+            _lib.check(rc, "b200vq_forward")
+        ctx.save_for_backward(znorm, zlen, idx, emb, wnorm)
+        ctx.cfg = (bool(l2norm), float(beta), float(w_cb), N, D, K, z.dtype, tuple(z.shape))
+        ctx.mark_non_differentiable(idx, hist, hist_first)
+        return znorm, emb, ste, idx, losses, hist, hist_first
+
+    @staticmethod
+    def backward(ctx, g_znorm, g_emb, g_ste, _g_idx, g_losses, _g_h, _g_hf):
+        znorm, zlen, idx, emb, wnorm = ctx.saved_tensors
+        l2norm, beta, w_cb, N, D, K, z_dtype, z_shape = ctx.cfg
+        lib = _lib.load()
+        dev = znorm.device
+
+        def _f32c(t):
+            return None if t is None else t.to(torch.float32).contiguous()
+
+        g_znorm, g_emb, g_ste, g_losses = _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste), _f32c(g_losses)
+        need_z, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        grad_z = grad_w = None
+        with torch.cuda.device(dev):
+            gz = torch.empty(z_shape, dtype=z_dtype, device=dev)
+            grad_emb = torch.empty(K, D, dtype=torch.float32, device=dev)
+            rc = lib.b200vq_backward(_ptr(g_ste), _ptr(g_znorm), _ptr(g_losses), znorm.data_ptr(), zlen.data_ptr(),
+                                     idx.data_ptr(), emb.data_ptr(), None, 0, N, D, K, int(l2norm), N, beta, w_cb,
+                                     gz.data_ptr(), _DTYPES[z_dtype], grad_emb.data_ptr(), _stream())
+            _lib.check(rc, "b200vq_backward")
+            if need_z:
+                grad_z = gz
+            if need_w:
+                grad_w = torch.empty(K, D, dtype=torch.float32, device=dev)
+                rc = lib.b200vq_codebook_backward(grad_emb.data_ptr(), _ptr(g_emb), emb.data_ptr(), wnorm.data_ptr(),
+                                                  K, D, int(l2norm), grad_w.data_ptr(), _stream())
+                _lib.check(rc, "b200vq_codebook_backward")
+        return grad_z, grad_w, None, None, None, None, None, None, None, None
+
+
+def vq_quantize(z, weight, *, mode, l2norm, t_inv=1.0, beta=0.25, w_cb=1.0, n_first=None, seed=0, offset=0):
+    """Fused quantizer step.  Returns (znorm, emb, ste, idx(N,), losses(3)=[loss_q,
+    loss_commit, loss_codebook], hist(K) int32, hist_first(K) int32)."""
+    if n_first is None:
+        n_first = z.shape[1] if z.dim() == 3 else z.shape[0]
+    return _VQFunction.apply(z, weight, int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb),
+                             int(n_first), int(seed), int(offset))
+
+
+def codebook_lookup(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, shape=None) -> torch.Tensor:
+    """get_codebook_entry (bottleneck.py:327-341) through b200vq_decode."""
+    _require_cuda(indices, "indices")
+    _require_cuda(weight, "embedding.weight")
+    lib = _lib.load()
+    idx = indices.reshape(-1).to(torch.int64).contiguous()
+    w = weight.detach().contiguous()
+    K, D = w.shape
+    out = torch.empty(idx.numel(), D, dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check(lib.b200vq_decode(idx.data_ptr(), idx.numel(), w.data_ptr(), K, D, int(l2norm), out.data_ptr(),
+                                     None, _stream()), "b200vq_decode")
+    return out.reshape(shape) if shape is not None else out.reshape(*indices.shape, D)
+
+
+def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Tensor:
+    """(4,) fp32 device tensor: index_usage, index_usage_batch, kl_uni, perplexity
+    (trainers/larp_tokenizer_trainer.py:335-352), no host sync."""
+    _require_cuda(hist_first, "hist_first")
+    lib = _lib.load()
+    out = torch.empty(4, dtype=torch.float32, device=hist_first.device)
+    with torch.cuda.device(hist_first.device):
+        _lib.check(lib.b200vq_usage_stats(hist_first.data_ptr(), hist_batch.data_ptr(), hist_first.numel(),
+                                          out.data_ptr(), _stream()), "b200vq_usage_stats")
+    return out
