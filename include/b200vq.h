@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 100
+#define B200VQ_VERSION 101
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -99,6 +99,32 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
                           int64_t row_offset, uint64_t* keys, b200vq_stream_t stream);
 
 /*
+ * Tensor-core (tcgen05) scoring path.  Same contract as b200vq_scores_partial -- keys[] get
+ * the per-row winner -- but the N x K contraction runs on the 5th-gen tensor cores with
+ * split-bf16 operands (error <= 1.2e-5 on unit vectors) and the accumulator tile in TMEM.
+ * Deterministic modes: rows whose best and second-best approximate scores are closer than
+ * 4e-5 are re-scored in exact fp32 inside the same call, so the indices are bit-identical
+ * to b200vq_scores_partial.  MODE_SAMPLE: lazy Gumbel-max over the approximate scores with
+ * the same per-(row, code) noise as the exact path.
+ *   b200vq_tc_supported   1 if (D, l2norm, mode) can take this path (D in {8,16,24,32}, l2norm)
+ *   b200vq_tc_image_bytes size of the codebook image for K codes
+ *   b200vq_prepare_codebook_tc  emb (K,D) fp32 normalised codebook -> image (16-byte aligned)
+ *   second      (N) fp32 scratch, zeroed by the caller with keys (deterministic modes)
+ *   n_resolved  nullable device counter, += number of rows re-scored exactly
+ *   k_offset    multiple of 256
+ */
+int b200vq_tc_supported(int D, int l2norm, int mode);
+size_t b200vq_tc_image_bytes(int64_t K, int D);
+int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, b200vq_stream_t stream);
+int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
+                     const void* image, const float* emb, const float* e2, int64_t K, int64_t k_offset,
+                     int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                     int64_t row_offset, uint64_t* keys, float* second, unsigned int* n_resolved,
+                     b200vq_stream_t stream);
+/* test aid: swap the LBO/SBO roles in the shared-memory matrix descriptors (probe only) */
+void b200vq_tc_debug_desc_swap(int swap);
+
+/*
  * Gather + straight-through + losses + usage histograms from keys
  * (bottleneck.py:292-298, :304-310; trainer bincounts larp_tokenizer_trainer.py:337-343).
  *   emb        full (K,D) normalised codebook (may be null when q_rows is given)
@@ -126,10 +152,13 @@ int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, i
 /*
  * One-call forward for the unsharded case: keys_reset + scores_partial(whole codebook) +
  * finish(finalize=1).  workspace >= b200vq_workspace_bytes(N,D,K); hist/hist_first/sqerr
- * are zeroed inside.
+ * are zeroed inside.  image: nullable tensor-core codebook image (b200vq_prepare_codebook_tc);
+ * when given and b200vq_tc_supported(D,l2norm,mode), scores come from b200vq_scores_tc,
+ * otherwise from the exact-fp32 b200vq_scores_partial.  Deterministic indices are identical
+ * either way.
  */
 int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
-                   const float* emb, const float* e2, int64_t K,
+                   const float* emb, const float* e2, const void* image, int64_t K,
                    int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
                    int64_t n_first, float beta, float w_cb,
                    float* znorm_out, float* ste_out, int64_t* idx_out, float* zlen_out,

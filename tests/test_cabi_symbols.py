@@ -26,10 +26,14 @@ def test_library_exports_every_declared_symbol():
 
 def test_host_only_entry_points():
     lib = _lib.load()
-    assert lib.b200vq_version() == 100
+    assert lib.b200vq_version() == 101
     assert lib.b200vq_max_dim() == 256
     assert lib.b200vq_error_string(0) == b"ok"
     assert lib.b200vq_error_string(-2) == b"unsupported code dimension"
     n = lib.b200vq_workspace_bytes(4096, 24, 8192)
     assert n >= 4096 * 8 + 16 and n % 256 == 0
     assert lib.b200vq_workspace_bytes(-1, 24, 8192) == 0
+    assert lib.b200vq_tc_supported(24, 1, 2) == 1 and lib.b200vq_tc_supported(64, 1, 0) == 0
+    assert lib.b200vq_tc_supported(16, 0, 0) == 0
+    assert lib.b200vq_tc_image_bytes(8192, 24) == 32 * 256 * 80 * 2
+    assert lib.b200vq_tc_image_bytes(300, 16) == 2 * 256 * 48 * 2

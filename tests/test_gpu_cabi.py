@@ -78,9 +78,9 @@ def test_invalid_arguments_return_codes():
                                      t.data_ptr(), _stream()) == -1
     assert lib.b200vq_scores_partial(t.data_ptr(), 0, 300, 4, 300, t.data_ptr(), t.data_ptr(), 4, 0, 0, 1, 1.0, 0, 0, 0,
                                      t.data_ptr(), _stream()) == -2
-    assert lib.b200vq_scores_partial(t.data_ptr(), 0, 16, 4, 16, t.data_ptr(), t.data_ptr(), 4, 2, 2, 1, 1.0, 0, 0, 0,
+    assert lib.b200vq_scores_partial(t.data_ptr(), 0, 16, 4, 16, t.data_ptr(), t.data_ptr(), 4, 4, 2, 1, 1.0, 0, 0, 0,
                                      t.data_ptr(), _stream()) == -3
-    assert lib.b200vq_forward(t.data_ptr(), 0, 16, 4, 16, t.data_ptr(), t.data_ptr(), 4, 0, 1, 1.0, 0, 0, 4, .25, 1., None,
+    assert lib.b200vq_forward(t.data_ptr(), 0, 16, 4, 16, t.data_ptr(), t.data_ptr(), None, 4, 0, 1, 1.0, 0, 0, 4, .25, 1., None,
                               None, None, None, None, None, None, None, 0, _stream()) == -5
     assert lib.b200vq_error_string(-5).decode().startswith("workspace")
     with pytest.raises(ValueError):

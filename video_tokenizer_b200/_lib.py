@@ -33,7 +33,13 @@ SIGNATURES = {
                                      _u64, _u64, _i64, _vp, _vp]),
     "b200vq_finish": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _i64, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp,
                              _vp, _vp, _vp, _i32, _i64, _f32, _f32, _vp, _vp]),
-    "b200vq_forward": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _i64, _i32, _i32, _f32, _u64, _u64,
+    "b200vq_tc_supported": (_i32, [_i32, _i32, _i32]),
+    "b200vq_tc_image_bytes": (_sz, [_i64, _i32]),
+    "b200vq_prepare_codebook_tc": (_i32, [_vp, _i64, _i32, _vp, _vp]),
+    "b200vq_scores_tc": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _f32, _u64, _u64,
+                                _i64, _vp, _vp, _vp, _vp]),
+    "b200vq_tc_debug_desc_swap": (None, [_i32]),
+    "b200vq_forward": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i32, _i32, _f32, _u64, _u64,
                               _i64, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b200vq_backward": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i64, _i32, _i64, _f32, _f32,
                                _vp, _i32, _vp, _vp]),
@@ -74,7 +80,7 @@ def load(build_if_missing: bool = True):
             except AttributeError as e:
                 raise B200VQError(f"{path} does not export {name}") from e
             fn.restype, fn.argtypes = res, args
-        if lib.b200vq_version() < 100:
+        if lib.b200vq_version() < 101:
             raise B200VQError("libb200vq.so is older than this Python package")
         _lib = lib
         return lib

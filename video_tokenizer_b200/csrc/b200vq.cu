@@ -1,8 +1,10 @@
 // b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
 #include "vq_generic.cuh"
+#include "vq_tc_kernel.cuh"
 
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdio>
 
 using namespace b200vq;
@@ -63,6 +65,22 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 
 }  // namespace
 
+namespace {
+template <int DD, typename T, int MM>
+int launch_tc(const TcParams& prm, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = tc_smem_bytes<DD>();
+    static bool configured = false;  // per instantiation
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(tc_scores_kernel<DD, T, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_check(e);
+        configured = true;
+    }
+    tc_scores_kernel<DD, T, MM><<<grid, kTcThreads, smem, st>>>(prm);
+    return launch_check();
+}
+}  // namespace
+
 extern "C" {
 
 int b200vq_version(void) { return B200VQ_VERSION; }
@@ -85,8 +103,9 @@ const char* b200vq_error_string(int code) {
 size_t b200vq_workspace_bytes(int64_t N, int D, int64_t K) {
     (void)D; (void)K;
     if (N < 0) return 0;
-    // [keys: N u64][scratch: sum + ticket, 2 doubles]
-    return align_up(static_cast<size_t>(N) * sizeof(uint64_t)) + align_up(2 * sizeof(double));
+    // [keys: N u64][scratch: sum + ticket, 2 doubles][runner-up scores: N f32][resolved-row counter]
+    return align_up(static_cast<size_t>(N) * sizeof(uint64_t)) + align_up(2 * sizeof(double)) +
+           align_up(static_cast<size_t>(N) * sizeof(float)) + align_up(sizeof(unsigned int));
 }
 
 int b200vq_prepare_codebook(const float* weight, int64_t K, int D, int l2norm, float* emb, float* e2,
@@ -114,7 +133,7 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
     if (N == 0 || K_local == 0) return B200VQ_OK;
     if (!z || !emb || !e2 || !keys || z_row_stride < D) return B200VQ_EINVAL;
     if (k_offset + K_local > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
-    if (mode == B200VQ_MODE_SAMPLE && (k_offset & 3)) return B200VQ_EALIGN;  // Philox groups of 4 codes
+    if (mode == B200VQ_MODE_SAMPLE && (k_offset & 7)) return B200VQ_EALIGN;  // noise groups of 8 codes
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
     if (specialised_dim(D)) {
@@ -144,7 +163,7 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
         int64_t splits = std::max<int64_t>(1, (want + row_tiles - 1) / row_tiles);
         splits = std::min<int64_t>(splits, (K_local + 63) / 64);
         int64_t per = (K_local + splits - 1) / splits;
-        per = (per + 3) / 4 * 4;
+        per = (per + 7) / 8 * 8;
         splits = (K_local + per - 1) / per;
         dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
         const size_t smem = static_cast<size_t>(64) * (D + 1) * sizeof(float);
@@ -159,6 +178,108 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
             });
         });
     }
+    return launch_check();
+}
+
+// ---- tensor-core path --------------------------------------------------------------------------
+static int g_tc_desc_swap = 0;
+void b200vq_tc_debug_desc_swap(int swap) { g_tc_desc_swap = swap; }
+
+int b200vq_tc_supported(int D, int l2norm, int mode) {
+    return tc_dim_ok(D) && l2norm && valid_mode(mode) ? 1 : 0;
+}
+
+size_t b200vq_tc_image_bytes(int64_t K, int D) {
+    if (K <= 0 || !tc_dim_ok(D)) return 0;
+    return static_cast<size_t>((K + kTcCodes - 1) / kTcCodes) * static_cast<size_t>(kTcCodes) * tc_kc(D) * 2;
+}
+
+int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, b200vq_stream_t stream) {
+    if (!emb || !image || K <= 0) return B200VQ_EINVAL;
+    if (!tc_dim_ok(D)) return B200VQ_EDIM;
+    if (reinterpret_cast<uintptr_t>(image) & 15) return B200VQ_EALIGN;
+    const unsigned blocks = static_cast<unsigned>((K + kTcCodes - 1) / kTcCodes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (D) {
+        case 8: prepare_codebook_tc_kernel<8><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 16: prepare_codebook_tc_kernel<16><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 24: prepare_codebook_tc_kernel<24><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        default: prepare_codebook_tc_kernel<32><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+    }
+    return launch_check();
+}
+
+
+int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const void* image,
+                     const float* emb, const float* e2, int64_t K, int64_t k_offset, int mode, int l2norm,
+                     float t_inv, uint64_t seed, uint64_t offset, int64_t row_offset, uint64_t* keys, float* second,
+                     unsigned int* n_resolved, b200vq_stream_t stream) {
+    if (N < 0 || K <= 0 || k_offset < 0 || row_offset < 0 || !valid_dtype(z_dtype) || !valid_mode(mode)) return B200VQ_EINVAL;
+    if (!tc_dim_ok(D)) return B200VQ_EDIM;
+    if (!l2norm) return B200VQ_EINVAL;  // the error bound assumes unit vectors
+    if (N == 0) return B200VQ_OK;
+    if (!z || !image || !keys || z_row_stride < D) return B200VQ_EINVAL;
+    if (mode != B200VQ_MODE_SAMPLE && (!emb || !e2 || !second)) return B200VQ_EINVAL;
+    if (k_offset & (kTcCodes - 1)) return B200VQ_EALIGN;
+    if (k_offset + K > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t row_tiles = (N + kTcRows - 1) / kTcRows;
+    const int total_tiles = static_cast<int>((K + kTcCodes - 1) / kTcCodes);
+    // code splits: fill the SMs, keep the last wave full, keep >= 4 tiles per CTA when possible
+    const int sms = sm_count();
+    int best_splits = 1;
+    double best_cost = 1e30;
+    for (int sp = 1; sp <= total_tiles; sp *= 2) {
+        const int per = (total_tiles + sp - 1) / sp;
+        if (sp > 1 && per < 4) break;
+        const int real = (total_tiles + per - 1) / per;
+        const double ctas = static_cast<double>(row_tiles) * real;
+        const double waves = std::ceil(ctas / sms);
+        const double cost = waves * (per + 1.5);  // 1.5 tiles ~ prologue/epilogue of a CTA
+        if (cost < best_cost) { best_cost = cost; best_splits = sp; }
+    }
+    const int per = (total_tiles + best_splits - 1) / best_splits;
+    const int splits = (total_tiles + per - 1) / per;
+    TcParams prm;
+    prm.z = z; prm.z_row_stride = z_row_stride; prm.N = N; prm.image = static_cast<const uint4*>(image);
+    prm.K = K; prm.k_offset = k_offset; prm.tiles_per_split = per; prm.l2norm = l2norm; prm.t_inv = t_inv;
+    prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
+    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = second; prm.desc_swap = g_tc_desc_swap;
+    dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+    int rc = B200VQ_OK;
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        switch (D) {
+            case 8: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<8, T, MM>(prm, grid, st); }); break; }
+            case 16: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<16, T, MM>(prm, grid, st); }); break; }
+            case 24: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<24, T, MM>(prm, grid, st); }); break; }
+            default: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<32, T, MM>(prm, grid, st); }); break; }
+        }
+    });
+    if (rc || mode == B200VQ_MODE_SAMPLE) return rc;
+    // exact re-scoring of undecided rows (deterministic modes)
+    const unsigned rblocks = static_cast<unsigned>(std::min<int64_t>((N + 255) / 256, 4ll * sms));
+    unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
+#define B200VQ_RESOLVE(DD, MM)                                                                                   \
+    resolve_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, emb, e2, K,    \
+                                                        k_offset, l2norm, k64, second, n_resolved)
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        if (mode == B200VQ_MODE_ARGMIN_DIST) {
+            switch (D) {
+                case 8: B200VQ_RESOLVE(8, B200VQ_MODE_ARGMIN_DIST); break;
+                case 16: B200VQ_RESOLVE(16, B200VQ_MODE_ARGMIN_DIST); break;
+                case 24: B200VQ_RESOLVE(24, B200VQ_MODE_ARGMIN_DIST); break;
+                default: B200VQ_RESOLVE(32, B200VQ_MODE_ARGMIN_DIST); break;
+            }
+        } else {
+            switch (D) {
+                case 8: B200VQ_RESOLVE(8, B200VQ_MODE_ARGMAX_COS); break;
+                case 16: B200VQ_RESOLVE(16, B200VQ_MODE_ARGMAX_COS); break;
+                case 24: B200VQ_RESOLVE(24, B200VQ_MODE_ARGMAX_COS); break;
+                default: B200VQ_RESOLVE(32, B200VQ_MODE_ARGMAX_COS); break;
+            }
+        }
+    });
+#undef B200VQ_RESOLVE
     return launch_check();
 }
 
@@ -196,7 +317,7 @@ int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, i
 }
 
 int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb,
-                   const float* e2, int64_t K, int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                   const float* e2, const void* image, int64_t K, int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
                    int64_t n_first, float beta, float w_cb, float* znorm_out, float* ste_out, int64_t* idx_out,
                    float* zlen_out, int32_t* hist, int32_t* hist_first, float* losses, void* workspace,
                    size_t workspace_bytes, b200vq_stream_t stream) {
@@ -210,8 +331,16 @@ int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, 
     if (rc) return rc;
     if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
     if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
-    rc = b200vq_scores_partial(z, z_dtype, z_row_stride, N, D, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
-                               keys, stream);
+    if (image && b200vq_tc_supported(D, l2norm, mode)) {
+        char* base = static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double));
+        float* second = reinterpret_cast<float*>(base);
+        unsigned int* n_resolved = reinterpret_cast<unsigned int*>(base + align_up(static_cast<size_t>(N) * sizeof(float)));
+        rc = b200vq_scores_tc(z, z_dtype, z_row_stride, N, D, image, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
+                              keys, second, n_resolved, stream);
+    } else {
+        rc = b200vq_scores_partial(z, z_dtype, z_row_stride, N, D, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
+                                   keys, stream);
+    }
     if (rc) return rc;
     return b200vq_finish(z, z_dtype, z_row_stride, N, D, emb, K, keys, nullptr, l2norm, n_first, znorm_out, ste_out, idx_out,
                          zlen_out, hist, hist_first, scratch, 1, N, beta, w_cb, losses, stream);

@@ -55,15 +55,58 @@ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint3
     }
     return {c0, c1, c2, c3};
 }
-// Standard Gumbel noise from 32 random bits: g = -log(E), E = -log(1-w) ~ Exp(1),
-// w = (bits+0.5)*2^-32.  log1p keeps the E -> 0 tail (the large-g tail that decides rare
-// wins) at full 32-bit resolution: g in [-2.8, 22.9].
-__device__ __forceinline__ float gumbel_from_bits(uint32_t bits) {
-    float w = (static_cast<float>(bits >> 1) + 0.5f) * 4.656612873077393e-10f;  // 2^-31
-    w = fminf(w, 0.99999994f);  // float(bits>>1) can round up to 2^31
-    const float e = -log1pf(-w);
-    return -__logf(e);
+// ---- Gumbel noise, generated per GROUP of 8 consecutive codes --------------------------------
+// The noise of code k for token row i is a pure function of (seed, offset, i, k) so draws do
+// not depend on tiling or sharding.  It is built hierarchically so that a whole group can be
+// ruled out from ONE draw (the tensor-core sampler does that, vq_tc.cuh):
+//   word_M  = Philox(stream 0; group>>2, row)[group&3]     -> E_M ~ Exp(1)
+//   M       = -log(E_M / 8)          the largest of the group's 8 iid Gumbels ~ Gumbel(log 8)
+//   J       = word_M & 7             its position (uniform; the low bits do not move M)
+//   word_p  = Philox(stream 1|2; group, row)[p]            -> E_p ~ Exp(1),  p != J
+//   g_p     = -log(E_M / 8 + E_p)    the other seven, iid Gumbel conditioned on being < M
+// (max of n iid Gumbels is Gumbel(log n) at a uniform position, the rest are Gumbels
+// truncated below it; P(g <= x | g <= M) = exp(-(e^-x - e^-M)).)
+constexpr uint32_t kNoiseGroup = 8;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// Exp(1) variate from 32 random bits, full relative resolution near 0 (the large-Gumbel tail).
+__device__ __forceinline__ float exp1_from_bits(uint32_t bits) {
+    float w = fmaf(static_cast<float>(bits), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // (bits+.5)/2^32
+    w = fminf(w, 0.99999994f);
+    const float series = fmaf(w, 0.5f * w, w);             // -log(1-w) for tiny w
+    const float direct = -kLn2 * __log2f(1.0f - w);
+    return w < 9.765625e-4f ? series : direct;
 }
+__device__ __forceinline__ float neg_log(float e) { return -kLn2 * __log2f(e); }
+
+__device__ __forceinline__ uint32_t noise_c3(uint64_t offset, uint32_t stream) {
+    return (static_cast<uint32_t>(offset >> 32) & 0x3FFFFFFFu) | (stream << 30);
+}
+// the four group-maximum words of groups 4*(group>>2) .. +3
+__device__ __forceinline__ Philox4 group_max_words(uint32_t group_quad, uint32_t grow, uint64_t seed, uint64_t offset) {
+    return philox4x32_10(group_quad, grow, static_cast<uint32_t>(offset), noise_c3(offset, 0),
+                         static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+}
+__device__ __forceinline__ uint32_t pick_word(const Philox4& r, uint32_t i) {
+    return i == 0 ? r.x : i == 1 ? r.y : i == 2 ? r.z : r.w;
+}
+// all 8 Gumbels of one group (the exact kernels and the sampler's event path use this)
+__device__ __forceinline__ void group_noise(uint32_t group, uint32_t grow, uint64_t seed, uint64_t offset,
+                                            uint32_t word_m, float (&g)[8]) {
+    const float em8 = 0.125f * exp1_from_bits(word_m);
+    const uint32_t J = word_m & 7u;
+    const Philox4 a = philox4x32_10(group, grow, static_cast<uint32_t>(offset), noise_c3(offset, 1),
+                                    static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    const Philox4 b = philox4x32_10(group, grow, static_cast<uint32_t>(offset), noise_c3(offset, 2),
+                                    static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const float e = static_cast<uint32_t>(p) == J ? 0.f : exp1_from_bits(w[p]);
+        g[p] = neg_log(em8 + e);
+    }
+}
+__device__ __forceinline__ float group_max_noise(uint32_t word_m) { return neg_log(0.125f * exp1_from_bits(word_m)); }
 
 // ---- reductions -----------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -125,13 +125,16 @@ __global__ void __launch_bounds__(128) scores_kernel(const T* __restrict__ z, in
         }
         __syncthreads();
 
-        for (int kk = 0; kk < cnt; kk += 4) {
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        constexpr int STEP = MODE == B200VQ_MODE_SAMPLE ? 8 : 4;
+        for (int kk = 0; kk < cnt; kk += STEP) {
+            float acc[STEP];
+#pragma unroll
+            for (int j = 0; j < STEP; ++j) acc[j] = 0.f;
             if (D % 4 == 0) {
 #pragma unroll
                 for (int d = 0; d < D; d += 4) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
+                    for (int j = 0; j < STEP; ++j) {
                         const float4 e = *reinterpret_cast<const float4*>(&s_e[(kk + j) * D + d]);
                         acc[j] = fmaf(zn[d + 0], e.x, acc[j]);
                         acc[j] = fmaf(zn[d + 1], e.y, acc[j]);
@@ -143,20 +146,18 @@ __global__ void __launch_bounds__(128) scores_kernel(const T* __restrict__ z, in
 #pragma unroll
                 for (int d = 0; d < D; ++d) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[j] = fmaf(zn[d], s_e[(kk + j) * D + d], acc[j]);
+                    for (int j = 0; j < STEP; ++j) acc[j] = fmaf(zn[d], s_e[(kk + j) * D + d], acc[j]);
                 }
             }
-            float g[4] = {0.f, 0.f, 0.f, 0.f};
+            float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (MODE == B200VQ_MODE_SAMPLE) {
-                const uint64_t kg = static_cast<uint64_t>(k_offset + kt + kk);
-                const Philox4 r = philox4x32_10(static_cast<uint32_t>(kg >> 2), grow, static_cast<uint32_t>(offset),
-                                                static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed),
-                                                static_cast<uint32_t>(seed >> 32));
-                g[0] = gumbel_from_bits(r.x); g[1] = gumbel_from_bits(r.y);
-                g[2] = gumbel_from_bits(r.z); g[3] = gumbel_from_bits(r.w);
+                // k_offset, kt and kk are multiples of 8: one noise group per step
+                const uint32_t group = static_cast<uint32_t>(static_cast<uint64_t>(k_offset + kt + kk) >> 3);
+                const Philox4 mw = group_max_words(group >> 2, grow, seed, offset);
+                group_noise(group, grow, seed, offset, pick_word(mw, group & 3u), g);
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < STEP; ++j) {
                 const float v = rank_value<MODE>(acc[j], z2, s_e2[kk + j], t_inv, g[j]);
                 if (kk + j < cnt && v > best_v) {
                     best_v = v;
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(64) scores_generic_kernel(const T* __restrict_
     float best_v = -INFINITY;
     uint32_t best_k = static_cast<uint32_t>(k_offset + k_begin);
     const uint32_t grow = static_cast<uint32_t>(row_offset + row);
-    Philox4 r = {0, 0, 0, 0};
+    float gn[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int64_t k = k_begin; k < k_end; ++k) {
         const float* e = emb + k * D;
         float acc = 0.f;
@@ -204,12 +205,12 @@ __global__ void __launch_bounds__(64) scores_generic_kernel(const T* __restrict_
         float g = 0.f;
         if (MODE == B200VQ_MODE_SAMPLE) {
             const uint64_t kg = static_cast<uint64_t>(k_offset + k);
-            if ((kg & 3) == 0 || k == k_begin)
-                r = philox4x32_10(static_cast<uint32_t>(kg >> 2), grow, static_cast<uint32_t>(offset),
-                                  static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed),
-                                  static_cast<uint32_t>(seed >> 32));
-            const uint32_t bits = (kg & 3) == 0 ? r.x : (kg & 3) == 1 ? r.y : (kg & 3) == 2 ? r.z : r.w;
-            g = gumbel_from_bits(bits);
+            if ((kg & 7) == 0 || k == k_begin) {
+                const uint32_t group = static_cast<uint32_t>(kg >> 3);
+                const Philox4 mw = group_max_words(group >> 2, grow, seed, offset);
+                group_noise(group, grow, seed, offset, pick_word(mw, group & 3u), gn);
+            }
+            g = gn[kg & 7];
         }
         const float v = rank_value<MODE>(acc, z2, __ldg(e2 + k), t_inv, g);
         if (v > best_v) { best_v = v; best_k = static_cast<uint32_t>(k_offset + k); }

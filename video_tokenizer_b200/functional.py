@@ -6,6 +6,7 @@ are not on a CUDA device raise.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -14,6 +15,19 @@ from . import _lib
 
 _DTYPES = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16, torch.float16: _lib.DT_F16}
 _workspaces: dict = {}
+
+# "tc": tcgen05 tensor-core scoring where supported (default); "exact": fp32 CUDA-core scoring.
+# Deterministic indices are identical either way (tests/test_gpu_tc.py).
+SCORING = os.environ.get("B200VQ_SCORING", "tc")
+
+
+def set_scoring(kind: str) -> str:
+    """Select the scoring kernels: "tc" (tensor cores, default) or "exact" (fp32 CUDA cores)."""
+    global SCORING
+    if kind not in ("tc", "exact"):
+        raise ValueError("scoring must be 'tc' or 'exact'")
+    prev, SCORING = SCORING, kind
+    return prev
 
 
 def _require_cuda(t: torch.Tensor, name: str):
@@ -80,6 +94,21 @@ def prepare_codebook(weight: torch.Tensor, l2norm: bool):
     return emb, e2, wnorm
 
 
+def prepare_codebook_tc(emb: torch.Tensor) -> Optional[torch.Tensor]:
+    """Split-bf16 tile image of the normalised codebook for the tcgen05 path, or None when the
+    code dimension has no tensor-core specialisation."""
+    K, D = emb.shape
+    lib = _lib.load()
+    nbytes = lib.b200vq_tc_image_bytes(K, D)
+    if nbytes == 0:
+        return None
+    image = torch.empty(nbytes, dtype=torch.uint8, device=emb.device)
+    with torch.cuda.device(emb.device):
+        _lib.check(lib.b200vq_prepare_codebook_tc(emb.data_ptr(), K, D, image.data_ptr(), _stream()),
+                   "b200vq_prepare_codebook_tc")
+    return image
+
+
 class _VQFunction(torch.autograd.Function):
     """forward = b200vq_prepare_codebook + b200vq_forward; backward = b200vq_backward +
     b200vq_codebook_backward.  Outputs: znorm, emb, ste, idx, losses(3), hist, hist_first."""
@@ -100,6 +129,9 @@ class _VQFunction(torch.autograd.Function):
         N = zz.shape[:-1].numel()
         with torch.cuda.device(dev):
             emb, e2, wnorm = prepare_codebook(weight, l2norm)
+            image = None
+            if SCORING == "tc" and lib.b200vq_tc_supported(D, int(l2norm), mode):
+                image = prepare_codebook_tc(emb)
             znorm = torch.empty(*z.shape, dtype=torch.float32, device=dev)
             ste = torch.empty(*z.shape, dtype=torch.float32, device=dev)
             idx = torch.empty(N, dtype=torch.int64, device=dev)
@@ -109,8 +141,8 @@ class _VQFunction(torch.autograd.Function):
             losses = torch.empty(3, dtype=torch.float32, device=dev)
             nbytes = lib.b200vq_workspace_bytes(N, D, K)
             ws = _workspace(dev, nbytes)
-            rc = lib.b200vq_forward(zz.data_ptr(), _DTYPES[zz.dtype], stride, N, D, emb.data_ptr(), e2.data_ptr(), K,
-                                    mode, int(l2norm), float(t_inv), seed, offset, int(n_first), float(beta),
+            rc = lib.b200vq_forward(zz.data_ptr(), _DTYPES[zz.dtype], stride, N, D, emb.data_ptr(), e2.data_ptr(),
+                                    _ptr(image), K, mode, int(l2norm), float(t_inv), seed, offset, int(n_first), float(beta),
                                     float(w_cb), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(),
                                     hist.data_ptr(), hist_first.data_ptr(), losses.data_ptr(), ws.data_ptr(),
                                     ws.numel(), _stream())

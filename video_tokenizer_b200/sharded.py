@@ -46,9 +46,9 @@ def allreduce_max_keys(keys: torch.Tensor, group=None) -> torch.Tensor:
     return keys
 
 
-def shard_bounds(K: int, world: int, rank: int, align: int = 4) -> Tuple[int, int]:
+def shard_bounds(K: int, world: int, rank: int, align: int = 8) -> Tuple[int, int]:
     """[begin, end) of the code slice rank owns; slice starts are multiples of ``align``
-    (Philox noise is generated for groups of 4 consecutive codes)."""
+    (sampling noise is generated for groups of 8 consecutive codes)."""
     per = -(-K // world)
     per = -(-per // align) * align
     b = min(K, rank * per)
