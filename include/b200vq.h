@@ -121,8 +121,6 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
                      int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
                      int64_t row_offset, uint64_t* keys, float* second, unsigned int* n_resolved,
                      b200vq_stream_t stream);
-/* test aid: swap the LBO/SBO roles in the shared-memory matrix descriptors (probe only) */
-void b200vq_tc_debug_desc_swap(int swap);
 
 /*
  * Gather + straight-through + losses + usage histograms from keys

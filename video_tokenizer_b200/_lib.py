@@ -38,7 +38,6 @@ SIGNATURES = {
     "b200vq_prepare_codebook_tc": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "b200vq_scores_tc": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _f32, _u64, _u64,
                                 _i64, _vp, _vp, _vp, _vp]),
-    "b200vq_tc_debug_desc_swap": (None, [_i32]),
     "b200vq_forward": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i32, _i32, _f32, _u64, _u64,
                               _i64, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b200vq_backward": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i64, _i32, _i64, _f32, _f32,

@@ -182,9 +182,6 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
 }
 
 // ---- tensor-core path --------------------------------------------------------------------------
-static int g_tc_desc_swap = 0;
-void b200vq_tc_debug_desc_swap(int swap) { g_tc_desc_swap = swap; }
-
 int b200vq_tc_supported(int D, int l2norm, int mode) {
     return tc_dim_ok(D) && l2norm && valid_mode(mode) ? 1 : 0;
 }
@@ -244,7 +241,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     prm.z = z; prm.z_row_stride = z_row_stride; prm.N = N; prm.image = static_cast<const uint4*>(image);
     prm.K = K; prm.k_offset = k_offset; prm.tiles_per_split = per; prm.l2norm = l2norm; prm.t_inv = t_inv;
     prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
-    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = second; prm.desc_swap = g_tc_desc_swap;
+    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = second;
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
     int rc = B200VQ_OK;
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {

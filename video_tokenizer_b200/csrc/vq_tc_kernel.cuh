@@ -48,7 +48,6 @@ struct TcParams {
     int64_t row_offset;
     unsigned long long* keys; // (N) merged with atomicMax
     float* second;            // (N) deterministic modes: runner-up approximate score, atomicMax on orderable bits
-    int desc_swap;            // debug: swap LBO/SBO roles (probe only)
 };
 
 // ---- deterministic epilogue: running top-2 of the approximate scores ---------------------------
@@ -224,8 +223,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         // ===== MMA issuer =====================================================================================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTcCodes);
-            const uint32_t a_lbo = p.desc_swap ? SBO : A_LBO, a_sbo = p.desc_swap ? A_LBO : SBO;
-            const uint32_t b_lbo = p.desc_swap ? SBO : B_LBO, b_sbo = p.desc_swap ? B_LBO : SBO;
             for (int i = 0; i < ntiles; ++i) {
                 const int buf = i & 1, s = i % kTcStages;
                 mbar_wait(bar_tempty + 8 * buf, ((i >> 1) & 1) ^ 1);
@@ -234,8 +231,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + s * B_BYTES);
 #pragma unroll
                 for (int k = 0; k < KC / 16; ++k) {
-                    umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, a_lbo, a_sbo),
-                              umma_desc(b0 + k * 2 * B_LBO, b_lbo, b_sbo), idesc, k > 0);
+                    umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
+                              umma_desc(b0 + k * 2 * B_LBO, B_LBO, SBO), idesc, k > 0);
                 }
                 umma_commit(bar_empty + 8 * s);     // stage reusable once these MMAs have read it
                 umma_commit(bar_tfull + 8 * buf);   // accumulator buffer ready for its epilogue group
