@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 
 using namespace b200vq;
 
@@ -198,10 +199,10 @@ int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, 
     const unsigned blocks = static_cast<unsigned>((K + kTcCodes - 1) / kTcCodes);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (D) {
-        case 8: prepare_codebook_tc_kernel<8><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        case 16: prepare_codebook_tc_kernel<16><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        case 24: prepare_codebook_tc_kernel<24><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        default: prepare_codebook_tc_kernel<32><<<blocks, 256, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 8: prepare_codebook_tc_kernel<8><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 16: prepare_codebook_tc_kernel<16><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 24: prepare_codebook_tc_kernel<24><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        default: prepare_codebook_tc_kernel<32><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
     }
     return launch_check();
 }
@@ -228,12 +229,17 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     double best_cost = 1e30;
     for (int sp = 1; sp <= total_tiles; sp *= 2) {
         const int per = (total_tiles + sp - 1) / sp;
-        if (sp > 1 && per < 4) break;
+        if (sp > 1 && per < 8) break;
         const int real = (total_tiles + per - 1) / per;
         const double ctas = static_cast<double>(row_tiles) * real;
         const double waves = std::ceil(ctas / sms);
-        const double cost = waves * (per + 1.5);  // 1.5 tiles ~ prologue/epilogue of a CTA
+        // ~3 tiles of prologue/teardown per CTA; a sampling CTA also re-learns the row maxima
+        const double cost = waves * (per + 3.0 + (mode == B200VQ_MODE_SAMPLE ? 4.0 : 0.0));
         if (cost < best_cost) { best_cost = cost; best_splits = sp; }
+    }
+    if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
+        const int v = std::atoi(env);
+        if (v >= 1 && v <= total_tiles) best_splits = v;
     }
     const int per = (total_tiles + best_splits - 1) / best_splits;
     const int splits = (total_tiles + per - 1) / per;

@@ -58,18 +58,21 @@ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint3
 // ---- Gumbel noise, generated per GROUP of 8 consecutive codes --------------------------------
 // The noise of code k for token row i is a pure function of (seed, offset, i, k) so draws do
 // not depend on tiling or sharding.  It is built hierarchically so that a whole group can be
-// ruled out from ONE draw (the tensor-core sampler does that, vq_tc.cuh):
-//   word_M  = Philox(stream 0; group>>2, row)[group&3]     -> E_M ~ Exp(1)
-//   M       = -log(E_M / 8)          the largest of the group's 8 iid Gumbels ~ Gumbel(log 8)
-//   J       = word_M & 7             its position (uniform; the low bits do not move M)
-//   word_p  = Philox(stream 1|2; group, row)[p]            -> E_p ~ Exp(1),  p != J
-//   g_p     = -log(E_M / 8 + E_p)    the other seven, iid Gumbel conditioned on being < M
+// ruled out from 16 random bits (the tensor-core sampler does that, vq_tc_kernel.cuh):
+//   hi16    = halfword (group & 7) of Philox(stream 0; group >> 3, row)
+//   a, b    = Philox(stream 1 | 2; group, row): words W0..W6 = a.xyzw, b.xyz ; b.w -> J, lo16
+//   E_M     = Exp(1) variate from the 32 bits (hi16 << 16 | lo16);  E_M >= hi16 / 2^16
+//   M       = -log(E_M / 8)      the largest of the group's 8 iid Gumbels ~ Gumbel(log 8)
+//   J       = b.w >> 29          its position (uniform)
+//   g_p     = -log(E_M / 8 + E_p), E_p ~ Exp(1) from the next unused word, p != J:
+//             the other seven, iid Gumbel conditioned on being < M
 // (max of n iid Gumbels is Gumbel(log n) at a uniform position, the rest are Gumbels
 // truncated below it; P(g <= x | g <= M) = exp(-(e^-x - e^-M)).)
 constexpr uint32_t kNoiseGroup = 8;
 constexpr float kLn2 = 0.6931471805599453f;
 
 // Exp(1) variate from 32 random bits, full relative resolution near 0 (the large-Gumbel tail).
+// Always >= w = (bits + 0.5) / 2^32 >= (bits >> 16) / 2^16.
 __device__ __forceinline__ float exp1_from_bits(uint32_t bits) {
     float w = fmaf(static_cast<float>(bits), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // (bits+.5)/2^32
     w = fminf(w, 0.99999994f);
@@ -82,31 +85,36 @@ __device__ __forceinline__ float neg_log(float e) { return -kLn2 * __log2f(e); }
 __device__ __forceinline__ uint32_t noise_c3(uint64_t offset, uint32_t stream) {
     return (static_cast<uint32_t>(offset >> 32) & 0x3FFFFFFFu) | (stream << 30);
 }
-// the four group-maximum words of groups 4*(group>>2) .. +3
-__device__ __forceinline__ Philox4 group_max_words(uint32_t group_quad, uint32_t grow, uint64_t seed, uint64_t offset) {
-    return philox4x32_10(group_quad, grow, static_cast<uint32_t>(offset), noise_c3(offset, 0),
+// the sixteen hi16 halfwords of groups 8*oct .. 8*oct+7 (two per word, low half first)
+__device__ __forceinline__ Philox4 group_head_words(uint32_t group_oct, uint32_t grow, uint64_t seed, uint64_t offset) {
+    return philox4x32_10(group_oct, grow, static_cast<uint32_t>(offset), noise_c3(offset, 0),
                          static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
 }
 __device__ __forceinline__ uint32_t pick_word(const Philox4& r, uint32_t i) {
     return i == 0 ? r.x : i == 1 ? r.y : i == 2 ? r.z : r.w;
 }
+__device__ __forceinline__ uint32_t head_hi16(const Philox4& r, uint32_t group) {
+    const uint32_t w = pick_word(r, (group & 7u) >> 1);
+    return (group & 1u) ? (w >> 16) : (w & 0xFFFFu);
+}
 // all 8 Gumbels of one group (the exact kernels and the sampler's event path use this)
 __device__ __forceinline__ void group_noise(uint32_t group, uint32_t grow, uint64_t seed, uint64_t offset,
-                                            uint32_t word_m, float (&g)[8]) {
-    const float em8 = 0.125f * exp1_from_bits(word_m);
-    const uint32_t J = word_m & 7u;
+                                            uint32_t hi16, float (&g)[8]) {
     const Philox4 a = philox4x32_10(group, grow, static_cast<uint32_t>(offset), noise_c3(offset, 1),
                                     static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
     const Philox4 b = philox4x32_10(group, grow, static_cast<uint32_t>(offset), noise_c3(offset, 2),
                                     static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
-    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    const uint32_t J = b.w >> 29;
+    const float em8 = 0.125f * exp1_from_bits((hi16 << 16) | (b.w & 0xFFFFu));
+    const uint32_t w[8] = {a.x, a.x, a.y, a.z, a.w, b.x, b.y, b.z};  // w[p] = W[p-1] (p >= 1)
+    const uint32_t v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.z};  // v[p] = W[p]   (p <= 6)
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
-        const float e = static_cast<uint32_t>(p) == J ? 0.f : exp1_from_bits(w[p]);
+        const uint32_t word = static_cast<uint32_t>(p) < J ? v[p] : w[p];
+        const float e = static_cast<uint32_t>(p) == J ? 0.f : exp1_from_bits(word);
         g[p] = neg_log(em8 + e);
     }
 }
-__device__ __forceinline__ float group_max_noise(uint32_t word_m) { return neg_log(0.125f * exp1_from_bits(word_m)); }
 
 // ---- reductions -----------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -153,8 +153,8 @@ __global__ void __launch_bounds__(128) scores_kernel(const T* __restrict__ z, in
             if (MODE == B200VQ_MODE_SAMPLE) {
                 // k_offset, kt and kk are multiples of 8: one noise group per step
                 const uint32_t group = static_cast<uint32_t>(static_cast<uint64_t>(k_offset + kt + kk) >> 3);
-                const Philox4 mw = group_max_words(group >> 2, grow, seed, offset);
-                group_noise(group, grow, seed, offset, pick_word(mw, group & 3u), g);
+                const Philox4 hw = group_head_words(group >> 3, grow, seed, offset);
+                group_noise(group, grow, seed, offset, head_hi16(hw, group), g);
             }
 #pragma unroll
             for (int j = 0; j < STEP; ++j) {
@@ -207,8 +207,8 @@ __global__ void __launch_bounds__(64) scores_generic_kernel(const T* __restrict_
             const uint64_t kg = static_cast<uint64_t>(k_offset + k);
             if ((kg & 7) == 0 || k == k_begin) {
                 const uint32_t group = static_cast<uint32_t>(kg >> 3);
-                const Philox4 mw = group_max_words(group >> 2, grow, seed, offset);
-                group_noise(group, grow, seed, offset, pick_word(mw, group & 3u), gn);
+                const Philox4 hw = group_head_words(group >> 3, grow, seed, offset);
+                group_noise(group, grow, seed, offset, head_hi16(hw, group), gn);
             }
             g = gn[kg & 7];
         }

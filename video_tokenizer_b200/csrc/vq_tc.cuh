@@ -16,10 +16,10 @@
 //     group's best perturbed score (vq_common.cuh: group noise); a group is expanded (its 8
 //     Gumbels generated) only if that bound beats the row's current best.
 //
-// Layout: one CTA = 128 token rows x a range of 256-code tiles.  Warps 0-3 / 4-7 are two
-// epilogue groups that drain alternate TMEM accumulator buffers (2 x 256 columns), warp 8
-// streams codebook tiles global->shared with cp.async.bulk (TMA engine) through a ring of
-// mbarrier-guarded stages, warp 9 issues the MMAs.  The codebook is pre-arranged in global
+// Layout: one CTA = 128 token rows x a range of 128-code tiles.  Warps 0-15 are four epilogue
+// groups, group g drains TMEM accumulator buffer g (4 x 128 columns) for tiles i = g mod 4;
+// warp 16 streams codebook tiles global->shared with cp.async.bulk (TMA engine) through a
+// ring of mbarrier-guarded stages, warp 17 issues the MMAs.  The codebook is pre-arranged in global
 // memory in exactly the shared-memory core-matrix order (prepare_codebook_tc_kernel), so a
 // tile is ONE contiguous bulk copy and no tensor map is needed.
 #pragma once
@@ -28,9 +28,11 @@
 namespace b200vq {
 
 constexpr int kTcRows = 128;       // token rows per CTA (UMMA M)
-constexpr int kTcCodes = 256;      // codes per tile (UMMA N)
-constexpr int kTcStages = 3;       // codebook tiles in flight
-constexpr int kTcThreads = 320;    // 8 epilogue warps + producer + MMA issuer
+constexpr int kTcCodes = 128;      // codes per tile (UMMA N)
+constexpr int kTcBufs = 4;         // TMEM accumulator buffers (4 x 128 columns), one per epilogue group
+constexpr int kTcStages = 4;       // codebook tiles in flight
+constexpr int kTcEpiWarps = 4 * kTcBufs;
+constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);  // 16 epilogue warps + producer + MMA issuer
 constexpr float kTcMargin = 4e-5f; // ambiguity window on approximate scores (see header)
 
 // contraction length of the split operands, padded to the UMMA K of 16
@@ -137,16 +139,16 @@ __device__ __forceinline__ uint16_t split_elem(const uint16_t (&hi)[D], const ui
 
 // =======================================================================================
 // Codebook image for the tensor-core path: for tile t, 16-byte K-chunk c, code r of the tile,
-// the 8 bf16 values live at ((t * (Kc/8) + c) * 256 + r) * 16 bytes -- the shared-memory
+// the 8 bf16 values live at ((t * (Kc/8) + c) * 128 + r) * 16 bytes -- the shared-memory
 // core-matrix order, so a tile is one contiguous bulk copy.  One thread per code.
 // =======================================================================================
 template <int D>
-__global__ void __launch_bounds__(256) prepare_codebook_tc_kernel(const float* __restrict__ emb, int64_t K,
+__global__ void __launch_bounds__(kTcCodes) prepare_codebook_tc_kernel(const float* __restrict__ emb, int64_t K,
                                                                   uint4* __restrict__ image) {
     constexpr int KC = tc_kc(D);
-    const int64_t code = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;  // padded to whole tiles
-    const int64_t tile = code >> 8;
-    const int r = static_cast<int>(code & 255);
+    const int64_t code = static_cast<int64_t>(blockIdx.x) * kTcCodes + threadIdx.x;  // padded to whole tiles
+    const int64_t tile = blockIdx.x;
+    const int r = threadIdx.x;
     uint16_t hi[D], lo[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) {
@@ -162,7 +164,7 @@ __global__ void __launch_bounds__(256) prepare_codebook_tc_kernel(const float* _
             const uint32_t b = split_elem<D, false>(hi, lo, c * 8 + 2 * e + 1);
             w[e] = a | (b << 16);
         }
-        image[(tile * (KC / 8) + c) * 256 + r] = make_uint4(w[0], w[1], w[2], w[3]);
+        image[(tile * (KC / 8) + c) * kTcCodes + r] = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 

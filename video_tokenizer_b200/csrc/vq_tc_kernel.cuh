@@ -1,4 +1,16 @@
 // b200vq -- the tcgen05 scoring kernel (see vq_tc.cuh for the design).
+//
+// Epilogue structure (both modes).  A thread owns one token row and sees its scores 32
+// columns at a time (tcgen05.ld 32x32b.x32).  Per group of 8 codes it does a few branch-free
+// instructions (3-input max tree + one compare) that decide whether the group can matter:
+//   deterministic: group max within kTcMargin of the row's best so far;
+//   stochastic:    16 random bits of the group's largest Gumbel say its bound can beat the
+//                  row's best perturbed score so far.
+// Groups that can matter are rare after the first few tiles, and rows of one warp hit them
+// at different times, so they are not processed in place (that would idle 31 lanes): the
+// lane pushes (group id, 8 scores) into its warp's shared-memory queue, and whenever 32
+// entries are queued the warp processes them one per lane with all lanes busy, merging
+// results into per-row keys in shared memory with atomics.
 #pragma once
 #include "vq_tc.cuh"
 
@@ -23,16 +35,15 @@ __device__ __forceinline__ float max8(const uint32_t* v) {
     const float c = fmaxf(__uint_as_float(v[6]), __uint_as_float(v[7]));
     return fmaxf(fmaxf(a, b), c);
 }
-__device__ __forceinline__ float key_value(unsigned long long key) {
-    const uint32_t o = static_cast<uint32_t>(key >> 32);
+__device__ __forceinline__ float ord_value(uint32_t o) {
     return __uint_as_float((o & 0x80000000u) ? (o ^ 0x80000000u) : ~o);
 }
-constexpr unsigned long long kKeyNegInf = 0x007FFFFFull << 32;  // orderable(-inf), no code
+__device__ __forceinline__ float key_value(unsigned long long key) { return ord_value(static_cast<uint32_t>(key >> 32)); }
+constexpr uint32_t kOrdNegInf = 0x007FFFFFu;                       // orderable(-inf)
+constexpr unsigned long long kKeyNegInf = 0x007FFFFFull << 32;     // (-inf, no code)
 
-struct TcSmem {
-    static constexpr int kQueueSlots = 64;   // per epilogue warp (ring)
-    static constexpr int kQueueWords = 12;   // 8 scores, group, row, 2 pad
-};
+constexpr int kQueueSlots = 64;   // per epilogue warp (ring); a push adds <= 32, a flush removes 32
+constexpr int kQueueWords = 12;   // 8 scores, group id, row | hi16 << 16, 2 pad (48-byte entries)
 
 struct TcParams {
     const void* z;
@@ -40,104 +51,123 @@ struct TcParams {
     int64_t N;
     const uint4* image;       // split-bf16 codebook image (prepare_codebook_tc_kernel)
     int64_t K;                // codes in the image
-    int64_t k_offset;         // global index of code 0 (multiple of 256)
+    int64_t k_offset;         // global index of code 0 (multiple of 128)
     int tiles_per_split;
     int l2norm;
     float t_inv;
     uint64_t seed, offset;
     int64_t row_offset;
     unsigned long long* keys; // (N) merged with atomicMax
-    float* second;            // (N) deterministic modes: runner-up approximate score, atomicMax on orderable bits
+    float* second;            // (N) deterministic modes: runner-up approximate score (orderable bits, atomicMax)
 };
 
-// ---- deterministic epilogue: running top-2 of the approximate scores ---------------------------
-struct DetState {
-    float best, second;
-    uint32_t idx;
-};
-__device__ __forceinline__ void det_chunk(const uint32_t (&v)[32], uint32_t code0, DetState& st) {
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        const float m = max8(&v[8 * g]);
-        if (m > st.best - kTcMargin) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float s = __uint_as_float(v[8 * g + j]);
-                st.second = fmaxf(st.second, fminf(s, st.best));
-                if (s > st.best) { st.best = s; st.idx = code0 + 8 * g + j; }
-            }
-        }
-    }
-}
-
-// ---- stochastic epilogue: lazy Gumbel-max ---------------------------------------------------------
-struct SampleCtx {
-    float* queue;                 // this warp's ring (kQueueSlots x kQueueWords floats)
-    unsigned long long* s_key;    // (128) per-row best key, shared by both epilogue groups
+// per-warp queue + per-row state shared by the epilogue warps of a CTA
+struct Epi {
+    float* queue;                 // this warp's ring
+    unsigned long long* s_key;    // (128) per-row best (value, code)
+    uint32_t* s_second;           // (128) per-row runner-up value, orderable bits (deterministic)
     uint32_t qhead, qtail;        // warp-uniform
-    float vstar;                  // this lane's row: best perturbed score so far
-    uint32_t row_local, grow;
+    uint32_t row_local, lane;
+    float thr;                    // lane's row: det = best - margin ; sample = 19.02 - vstar*log2(e)
+    // stochastic only
+    uint32_t grow0;               // global row id of local row 0
     float t_inv;
     uint64_t seed, offset;
-    int64_t k_end_global;         // first invalid global code
+    uint32_t k_end_global;
 };
 
-__device__ __forceinline__ void sample_flush(SampleCtx& c, uint32_t lane, uint32_t n) {
+constexpr float kLog2e = 1.4426950408889634f;
+
+// ---- deterministic: merge one queued group into its row's (best, runner-up) -----------------------
+__device__ __noinline__ void det_flush(const float* queue, uint32_t qhead, uint32_t n, uint32_t lane,
+                                       unsigned long long* s_key, uint32_t* s_second) {
     if (lane < n) {
-        const float* e = c.queue + ((c.qhead + lane) & (TcSmem::kQueueSlots - 1)) * TcSmem::kQueueWords;
+        const float* e = queue + ((qhead + lane) & (kQueueSlots - 1)) * kQueueWords;
         const float4 s0 = *reinterpret_cast<const float4*>(e);
         const float4 s1 = *reinterpret_cast<const float4*>(e + 4);
         const uint2 meta = *reinterpret_cast<const uint2*>(e + 8);
-        const uint32_t group = meta.x, rl = meta.y & 0xFFu, grow = c.grow - c.row_local + rl;
-        const Philox4 mw = group_max_words(group >> 2, grow, c.seed, c.offset);
+        const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+        float best = -INFINITY, sec = -INFINITY;
+        uint32_t bi = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            sec = fmaxf(sec, fminf(s[j], best));
+            if (s[j] > best) { best = s[j]; bi = j; }
+        }
+        const uint32_t rl = meta.y & 0xFFu;
+        const unsigned long long old = atomicMax(s_key + rl, make_key(best, meta.x * 8 + bi));
+        // the loser of every key comparison is a runner-up candidate
+        const float runner = fmaxf(sec, fminf(key_value(old), best));
+        atomicMax(s_second + rl, orderable(runner));
+    }
+    __syncwarp();
+}
+
+// ---- stochastic: expand one queued group (its 8 Gumbels) and merge its best perturbed score -------
+__device__ __noinline__ void sample_flush(const float* queue, uint32_t qhead, uint32_t n, uint32_t lane,
+                                          unsigned long long* s_key, uint32_t grow0, float t_inv, uint64_t seed,
+                                          uint64_t offset, uint32_t k_end_global) {
+    if (lane < n) {
+        const float* e = queue + ((qhead + lane) & (kQueueSlots - 1)) * kQueueWords;
+        const float4 s0 = *reinterpret_cast<const float4*>(e);
+        const float4 s1 = *reinterpret_cast<const float4*>(e + 4);
+        const uint2 meta = *reinterpret_cast<const uint2*>(e + 8);
+        const uint32_t group = meta.x, rl = meta.y & 0xFFu, hi16 = meta.y >> 16;
         float g[8];
-        group_noise(group, grow, c.seed, c.offset, pick_word(mw, group & 3u), g);
+        group_noise(group, grow0 + rl, seed, offset, hi16, g);
         const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
         float bv = -INFINITY;
         uint32_t bk = group * 8;
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
-            const float v = fmaf(s[p], c.t_inv, g[p]);
-            if (static_cast<int64_t>(group) * 8 + p < c.k_end_global && v > bv) { bv = v; bk = group * 8 + p; }
+            const float v = fmaf(s[p], t_inv, g[p]);
+            if (group * 8 + p < k_end_global && v > bv) { bv = v; bk = group * 8 + p; }
         }
-        atomicMax(c.s_key + rl, make_key(bv, bk));
+        atomicMax(s_key + rl, make_key(bv, bk));
     }
-    c.qhead += n;
     __syncwarp();
-    c.vstar = key_value(c.s_key[c.row_local]);
 }
 
-__device__ __forceinline__ void sample_chunk(const uint32_t (&v)[32], uint32_t code0_global, uint32_t lane, SampleCtx& c) {
-    // code0_global is a multiple of 32: groups 4q .. 4q+3 share one Philox call
-    const Philox4 mw = group_max_words(code0_global >> 5, c.grow, c.seed, c.offset);
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        const float m = max8(&v[8 * g]);
-        const float bound = fmaf(m, c.t_inv, group_max_noise(pick_word(mw, g)));
-        const bool ev = bound > c.vstar;
-        const uint32_t b = __ballot_sync(0xffffffffu, ev);
-        if (b) {
-            if (ev) {
-                const uint32_t slot = (c.qtail + __popc(b & ((1u << lane) - 1u))) & (TcSmem::kQueueSlots - 1);
-                float* e = c.queue + slot * TcSmem::kQueueWords;
-                *reinterpret_cast<uint4*>(e) = make_uint4(v[8 * g], v[8 * g + 1], v[8 * g + 2], v[8 * g + 3]);
-                *reinterpret_cast<uint4*>(e + 4) = make_uint4(v[8 * g + 4], v[8 * g + 5], v[8 * g + 6], v[8 * g + 7]);
-                *reinterpret_cast<uint2*>(e + 8) = make_uint2((code0_global >> 3) + g, c.row_local);
-            }
-            c.qtail += __popc(b);
-            __syncwarp();
-            if (c.qtail - c.qhead >= 32u) sample_flush(c, lane, 32u);
-        }
+template <bool SAMPLE>
+__device__ __forceinline__ void epi_flush(Epi& c, uint32_t n) {
+    if (SAMPLE) {
+        sample_flush(c.queue, c.qhead, n, c.lane, c.s_key, c.grow0, c.t_inv, c.seed, c.offset, c.k_end_global);
+        c.thr = fmaf(key_value(c.s_key[c.row_local]), -kLog2e, 19.02f);
+    } else {
+        det_flush(c.queue, c.qhead, n, c.lane, c.s_key, c.s_second);
+        c.thr = key_value(c.s_key[c.row_local]) - kTcMargin;
     }
+    c.qhead += n;
+}
+
+// push the groups flagged in this warp (ballot b) and drain the queue when 32 are waiting
+template <bool SAMPLE>
+__device__ __forceinline__ void epi_push(Epi& c, uint32_t b, bool ev, const uint32_t* v8, uint32_t group, uint32_t hi16) {
+    if (ev) {
+        const uint32_t slot = (c.qtail + __popc(b & ((1u << c.lane) - 1u))) & (kQueueSlots - 1);
+        float* e = c.queue + slot * kQueueWords;
+        *reinterpret_cast<uint4*>(e) = make_uint4(v8[0], v8[1], v8[2], v8[3]);
+        *reinterpret_cast<uint4*>(e + 4) = make_uint4(v8[4], v8[5], v8[6], v8[7]);
+        *reinterpret_cast<uint2*>(e + 8) = make_uint2(group, c.row_local | (hi16 << 16));
+    }
+    c.qtail += __popc(b);
+    __syncwarp();
+    if (c.qtail - c.qhead >= 32u) epi_flush<SAMPLE>(c, 32u);
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // =======================================================================================
-// grid = (row tiles of 128, code splits); block = 320 threads; dynamic smem = tc_smem_bytes(D, MODE)
+// grid = (row tiles of 128, code splits); block = 576 threads; dynamic smem = tc_smem_bytes<D>()
 // =======================================================================================
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
     return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_kc(D) * 2 + kTcStages * tc_tile_bytes(D) +
-           8 * TcSmem::kQueueSlots * TcSmem::kQueueWords * 4 + kTcRows * 8 + 3 * kTcRows * 4 + 256;
+           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + kTcRows * 4 + 256;
 }
 
 template <int D, typename T, int MODE>
@@ -153,21 +183,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     uint8_t* sA = smem;
     uint8_t* sB = sA + A_BYTES;
     float* s_queue = reinterpret_cast<float*>(sB + kTcStages * B_BYTES);
-    unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_queue + 8 * TcSmem::kQueueSlots * TcSmem::kQueueWords);
-    float* s_best = reinterpret_cast<float*>(s_key + kTcRows);
-    float* s_second = s_best + kTcRows;
-    uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_second + kTcRows);
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_idx + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 4);
+    unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_queue + kTcEpiWarps * kQueueSlots * kQueueWords);
+    uint32_t* s_second = reinterpret_cast<uint32_t*>(s_key + kTcRows);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_second + kTcRows);  // full[S], empty[S], tfull[4], tempty[4]
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 2 * kTcBufs);
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kTcRows;
     const int total_tiles = static_cast<int>((p.K + kTcCodes - 1) / kTcCodes);
     const int tile_begin = blockIdx.y * p.tiles_per_split;
     const int ntiles = min(p.tiles_per_split, total_tiles - tile_begin);
+    const uint32_t first_code = static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes;
 
     const uint32_t bar_full = smem_u32(s_bar), bar_empty = bar_full + 8 * kTcStages;
-    const uint32_t bar_tfull = bar_empty + 8 * kTcStages, bar_tempty = bar_tfull + 16;
+    const uint32_t bar_tfull = bar_empty + 8 * kTcStages, bar_tempty = bar_tfull + 8 * kTcBufs;
 
     // ---- prologue ---------------------------------------------------------------------------------
     if (threadIdx.x < kTcRows) {
@@ -192,14 +221,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                        (static_cast<uint32_t>(split_elem<D, true>(hi, lo, c * 8 + 2 * e + 1)) << 16);
             *reinterpret_cast<uint4*>(sA + c * A_LBO + threadIdx.x * 16) = make_uint4(w[0], w[1], w[2], w[3]);
         }
-        s_key[threadIdx.x] = kKeyNegInf;
-    } else if (warp == 8) {
+        s_key[threadIdx.x] = make_key(-INFINITY, first_code);
+        s_second[threadIdx.x] = kOrdNegInf;
+    } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTcStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-            for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 128); }
+            for (int b = 0; b < kTcBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 128); }
             fence_barrier_init();
         }
-    } else if (warp == 9) {
+    } else if (warp == kTcEpiWarps + 1) {
         tmem_alloc(smem_u32(s_tmem), 512);
     }
     fence_proxy_async();  // A tile (generic-proxy stores) -> visible to the tensor core (async proxy)
@@ -208,7 +238,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
 
-    if (warp == 8) {
+    if (warp == kTcEpiWarps) {
         // ===== codebook tile producer: one bulk copy per tile ========================================
         if (lane == 0) {
             const uint8_t* src = reinterpret_cast<const uint8_t*>(p.image) + static_cast<size_t>(tile_begin) * B_BYTES;
@@ -219,13 +249,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 bulk_g2s(smem_u32(sB + s * B_BYTES), src + static_cast<size_t>(i) * B_BYTES, B_BYTES, bar_full + 8 * s);
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == kTcEpiWarps + 1) {
         // ===== MMA issuer =====================================================================================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTcCodes);
             for (int i = 0; i < ntiles; ++i) {
-                const int buf = i & 1, s = i % kTcStages;
-                mbar_wait(bar_tempty + 8 * buf, ((i >> 1) & 1) ^ 1);
+                const int buf = i % kTcBufs, s = i % kTcStages;
+                mbar_wait(bar_tempty + 8 * buf, ((i / kTcBufs) & 1) ^ 1);
                 mbar_wait(bar_full + 8 * s, (i / kTcStages) & 1);
                 tc_fence_after();
                 const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + s * B_BYTES);
@@ -239,76 +269,76 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             }
         }
     } else {
-        // ===== epilogue groups (warps 0-3 drain buffer 0, warps 4-7 buffer 1) ==========================
+        // ===== epilogue groups: group g = warps 4g..4g+3 drains TMEM buffer g ================================
         const int grp = warp >> 2;
-        const uint32_t row_local = 32 * (warp & 3) + lane;
+        Epi c;
+        c.queue = s_queue + warp * kQueueSlots * kQueueWords;
+        c.s_key = s_key;
+        c.s_second = s_second;
+        c.qhead = c.qtail = 0;
+        c.row_local = 32 * (warp & 3) + lane;
+        c.lane = lane;
+        c.thr = SAMPLE ? INFINITY : -INFINITY;   // "everything can matter" until the first flush
+        c.grow0 = static_cast<uint32_t>(p.row_offset + row0);
+        c.t_inv = p.t_inv;
+        c.seed = p.seed;
+        c.offset = p.offset;
+        c.k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
         const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + grp * kTcCodes;
-        DetState det = {-INFINITY, -INFINITY, static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes};
-        SampleCtx sc;
-        if (SAMPLE) {
-            sc.queue = s_queue + warp * TcSmem::kQueueSlots * TcSmem::kQueueWords;
-            sc.s_key = s_key;
-            sc.qhead = sc.qtail = 0;
-            sc.vstar = -INFINITY;
-            sc.row_local = row_local;
-            sc.grow = static_cast<uint32_t>(p.row_offset + row0 + row_local);
-            sc.t_inv = p.t_inv;
-            sc.seed = p.seed;
-            sc.offset = p.offset;
-            sc.k_end_global = p.k_offset + p.K;
-        }
-        uint32_t va[32], vb[32];
-        for (int i = grp; i < ntiles; i += 2) {
-            mbar_wait(bar_tfull + 8 * grp, (i >> 1) & 1);
-            tc_fence_after();
-            const int64_t tile_code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes;  // local code index
+        const float tl2e = p.t_inv * kLog2e;
+        uint32_t v[32];
+        for (int i = grp; i < ntiles; i += kTcBufs) {
+            const int64_t tile_code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes;  // index within the image
+            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + tile_code0) >> 3);  // multiple of 16
             const int valid = static_cast<int>(min(static_cast<int64_t>(kTcCodes), p.K - tile_code0));
-            tmem_ld32(t_lane, va);
-#pragma unroll 1
-            for (int c = 0; c < kTcCodes / 32; c += 2) {
-                tmem_ld_wait32(va);
-                tmem_ld32(t_lane + (c + 1) * 32, vb);
-                if ((c + 1) * 32 > valid) {
+            uint32_t hi16[16];
+            if (SAMPLE) {   // 16 random bits per group, two Philox calls per tile, before the accumulator is needed
+                const Philox4 r0 = group_head_words(group0 >> 3, c.grow0 + c.row_local, p.seed, p.offset);
+                const Philox4 r1 = group_head_words((group0 >> 3) + 1, c.grow0 + c.row_local, p.seed, p.offset);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) if (c * 32 + j >= valid) va[j] = 0xFF800000u;
-                }
-                const uint32_t code_a = static_cast<uint32_t>(p.k_offset + tile_code0) + c * 32;
-                if (SAMPLE) sample_chunk(va, code_a, lane, sc); else det_chunk(va, code_a, det);
-                tmem_ld_wait32(vb);
-                if (c + 2 < kTcCodes / 32) tmem_ld32(t_lane + (c + 2) * 32, va);
-                if ((c + 2) * 32 > valid) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) if ((c + 1) * 32 + j >= valid) vb[j] = 0xFF800000u;
-                }
-                if (SAMPLE) sample_chunk(vb, code_a + 32, lane, sc); else det_chunk(vb, code_a + 32, det);
+                for (int q = 0; q < 8; ++q) { hi16[q] = head_hi16(r0, q); hi16[8 + q] = head_hi16(r1, q); }
             }
-            tc_fence_before();
-            mbar_arrive(bar_tempty + 8 * grp);
+            mbar_wait(bar_tfull + 8 * grp, (i / kTcBufs) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int ch = 0; ch < kTcCodes / 32; ++ch) {
+                tmem_ld32(t_lane + ch * 32, v);
+                tmem_ld_wait32(v);
+                if (ch == kTcCodes / 32 - 1) {   // accumulator buffer is in registers: hand it back to the MMA warp
+                    tc_fence_before();
+                    mbar_arrive(bar_tempty + 8 * grp);
+                }
+                if ((ch + 1) * 32 > valid) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) if (ch * 32 + j >= valid) v[j] = 0xFF800000u;
+                }
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const float m = max8(&v[8 * g]);
+                    bool ev;
+                    if (SAMPLE) {
+                        const float fh = __uint_as_float(0x4B000000u | hi16[4 * ch + g]) - 8388608.0f;
+                        ev = fh < ex2_approx(fmaf(m, tl2e, c.thr));
+                    } else {
+                        ev = m > c.thr;
+                    }
+                    const uint32_t b = __ballot_sync(0xffffffffu, ev);
+                    if (b) epi_push<SAMPLE>(c, b, ev, &v[8 * g], group0 + 4 * ch + g, SAMPLE ? hi16[4 * ch + g] : 0u);
+                }
+            }
         }
-        if (SAMPLE) {
-            while (sc.qtail != sc.qhead) sample_flush(sc, lane, min(32u, sc.qtail - sc.qhead));
-        } else if (grp == 1) {
-            s_best[row_local] = det.best; s_second[row_local] = det.second; s_idx[row_local] = det.idx;
-        }
-        // merge the two groups (named barrier over the 256 epilogue threads)
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        while (c.qtail != c.qhead) epi_flush<SAMPLE>(c, min(32u, c.qtail - c.qhead));
+        // all four groups done -> publish the rows (named barrier over the 512 epilogue threads)
+        asm volatile("bar.sync 1, 512;" ::: "memory");
         if (grp == 0) {
-            const int64_t row = row0 + row_local;
+            const int64_t row = row0 + c.row_local;
             if (row < p.N && ntiles > 0) {
-                if (SAMPLE) {
-                    atomicMax(p.keys + row, s_key[row_local]);
-                } else {
-                    const float ob = s_best[row_local], os = s_second[row_local];
-                    const uint32_t oi = s_idx[row_local];
-                    float best = det.best, second = fmaxf(det.second, os);
-                    uint32_t idx = det.idx;
-                    if (ob > best || (ob == best && oi < idx)) { second = fmaxf(second, best); best = ob; idx = oi; }
-                    else second = fmaxf(second, ob);
+                const unsigned long long mine = s_key[c.row_local];
+                const unsigned long long old = atomicMax(p.keys + row, mine);
+                if (!SAMPLE) {
                     // cross-split merge: the loser of every key comparison is a runner-up candidate
-                    const unsigned long long mine = make_key(best, idx);
-                    const unsigned long long old = atomicMax(p.keys + row, mine);
-                    float runner = second;
-                    if (old != 0ull) runner = fmaxf(runner, fminf(key_value(old), best));
+                    float runner = ord_value(s_second[c.row_local]);
+                    if (old != 0ull) runner = fmaxf(runner, fminf(key_value(old), key_value(mine)));
                     atomicMax(reinterpret_cast<unsigned int*>(p.second) + row, orderable(runner));
                 }
             }
@@ -317,20 +347,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     // ---- teardown ------------------------------------------------------------------------------------
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) tmem_dealloc(tmem_base, 512);
+    if (warp == kTcEpiWarps + 1) tmem_dealloc(tmem_base, 512);
 }
 
-}  // namespace b200vq
-
-namespace b200vq {
-
-// =======================================================================================
-// Exact re-scoring of the rows the tensor-core pass could not decide (runner-up within
-// kTcMargin of the best approximate score).  Same fp32 arithmetic as scores_kernel, so the
-// final indices are bit-identical to the exact path.  Each CTA owns a contiguous range of
-// rows, collects the undecided ones 256 at a time and re-scans the codebook for each with
-// all 256 threads.
-// =======================================================================================
 template <int D, typename T, int MODE>
 __global__ void __launch_bounds__(256) resolve_kernel(const T* __restrict__ z, int64_t z_row_stride, int64_t N,
                                                       const float* __restrict__ emb, const float* __restrict__ e2,
