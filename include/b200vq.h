@@ -111,7 +111,7 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
  *   b200vq_prepare_codebook_tc  emb (K,D) fp32 normalised codebook -> image (16-byte aligned)
  *   second      (N) fp32 scratch, zeroed by the caller with keys (deterministic modes)
  *   n_resolved  nullable device counter, += number of rows re-scored exactly
- *   k_offset    multiple of 128
+ *   k_offset    multiple of 256
  */
 int b200vq_tc_supported(int D, int l2norm, int mode);
 size_t b200vq_tc_image_bytes(int64_t K, int D);

@@ -35,5 +35,5 @@ def test_host_only_entry_points():
     assert lib.b200vq_workspace_bytes(-1, 24, 8192) == 0
     assert lib.b200vq_tc_supported(24, 1, 2) == 1 and lib.b200vq_tc_supported(64, 1, 0) == 0
     assert lib.b200vq_tc_supported(16, 0, 0) == 0
-    assert lib.b200vq_tc_image_bytes(8192, 24) == 32 * 256 * 80 * 2
-    assert lib.b200vq_tc_image_bytes(300, 16) == 3 * 128 * 48 * 2
+    assert lib.b200vq_tc_image_bytes(8192, 24) == 32 * 256 * 6 * 16 + 16
+    assert lib.b200vq_tc_image_bytes(300, 16) == 2 * 256 * 4 * 16 + 16

@@ -189,7 +189,8 @@ int b200vq_tc_supported(int D, int l2norm, int mode) {
 
 size_t b200vq_tc_image_bytes(int64_t K, int D) {
     if (K <= 0 || !tc_dim_ok(D)) return 0;
-    return static_cast<size_t>((K + kTcCodes - 1) / kTcCodes) * static_cast<size_t>(kTcCodes) * tc_kc(D) * 2;
+    // tiles, then one 16-byte trailer holding the "codebook has a non-unit row" flag word
+    return static_cast<size_t>((K + kTcCodes - 1) / kTcCodes) * tc_tile_bytes(D) + 16;
 }
 
 int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, b200vq_stream_t stream) {
@@ -198,11 +199,15 @@ int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, 
     if (reinterpret_cast<uintptr_t>(image) & 15) return B200VQ_EALIGN;
     const unsigned blocks = static_cast<unsigned>((K + kTcCodes - 1) / kTcCodes);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint4* img = static_cast<uint4*>(image);
+    unsigned int* flags = reinterpret_cast<unsigned int*>(static_cast<char*>(image) + static_cast<size_t>(blocks) * tc_tile_bytes(D));
+    int rc = cuda_check(cudaMemsetAsync(flags, 0, 16, st));
+    if (rc) return rc;
     switch (D) {
-        case 8: prepare_codebook_tc_kernel<8><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        case 16: prepare_codebook_tc_kernel<16><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        case 24: prepare_codebook_tc_kernel<24><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
-        default: prepare_codebook_tc_kernel<32><<<blocks, kTcCodes, 0, st>>>(emb, K, static_cast<uint4*>(image)); break;
+        case 8: prepare_codebook_tc_kernel<8><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        case 16: prepare_codebook_tc_kernel<16><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        case 24: prepare_codebook_tc_kernel<24><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        default: prepare_codebook_tc_kernel<32><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
     }
     return launch_check();
 }
@@ -229,12 +234,12 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     double best_cost = 1e30;
     for (int sp = 1; sp <= total_tiles; sp *= 2) {
         const int per = (total_tiles + sp - 1) / sp;
-        if (sp > 1 && per < 8) break;
+        if (sp > 1 && per < 4) break;
         const int real = (total_tiles + per - 1) / per;
         const double ctas = static_cast<double>(row_tiles) * real;
         const double waves = std::ceil(ctas / sms);
-        // ~3 tiles of prologue/teardown per CTA; a sampling CTA also re-learns the row maxima
-        const double cost = waves * (per + 3.0 + (mode == B200VQ_MODE_SAMPLE ? 4.0 : 0.0));
+        // ~1.5 tiles of prologue/teardown per CTA; a sampling CTA also re-learns the row maxima
+        const double cost = waves * (per + 1.5 + (mode == B200VQ_MODE_SAMPLE ? 2.0 : 0.0));
         if (cost < best_cost) { best_cost = cost; best_splits = sp; }
     }
     if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
@@ -248,6 +253,8 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     prm.K = K; prm.k_offset = k_offset; prm.tiles_per_split = per; prm.l2norm = l2norm; prm.t_inv = t_inv;
     prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
     prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = second;
+    prm.debug = 0;
+    if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
     int rc = B200VQ_OK;
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
@@ -258,13 +265,15 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
             default: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<32, T, MM>(prm, grid, st); }); break; }
         }
     });
-    if (rc || mode == B200VQ_MODE_SAMPLE) return rc;
+    if (rc || mode == B200VQ_MODE_SAMPLE || prm.debug) return rc;
     // exact re-scoring of undecided rows (deterministic modes)
+    const unsigned int* flags = reinterpret_cast<const unsigned int*>(
+        static_cast<const char*>(image) + static_cast<size_t>(total_tiles) * tc_tile_bytes(D));
     const unsigned rblocks = static_cast<unsigned>(std::min<int64_t>((N + 255) / 256, 4ll * sms));
     unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
 #define B200VQ_RESOLVE(DD, MM)                                                                                   \
     resolve_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, emb, e2, K,    \
-                                                        k_offset, l2norm, k64, second, n_resolved)
+                                                        k_offset, l2norm, k64, second, flags, n_resolved)
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
         if (mode == B200VQ_MODE_ARGMIN_DIST) {
             switch (D) {

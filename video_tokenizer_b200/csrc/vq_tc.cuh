@@ -16,29 +16,38 @@
 //     group's best perturbed score (vq_common.cuh: group noise); a group is expanded (its 8
 //     Gumbels generated) only if that bound beats the row's current best.
 //
-// Layout: one CTA = 128 token rows x a range of 128-code tiles.  Warps 0-15 are four epilogue
-// groups, group g drains TMEM accumulator buffer g (4 x 128 columns) for tiles i = g mod 4;
-// warp 16 streams codebook tiles global->shared with cp.async.bulk (TMA engine) through a
-// ring of mbarrier-guarded stages, warp 17 issues the MMAs.  The codebook is pre-arranged in global
-// memory in exactly the shared-memory core-matrix order (prepare_codebook_tc_kernel), so a
-// tile is ONE contiguous bulk copy and no tensor map is needed.
+// Layout: one CTA = 128 token rows x a range of 256-code tiles.  Warps 0-15 are four epilogue
+// groups; group g drains columns [128*(g&1), +128) of TMEM accumulator buffer g>>1 (2 x 256
+// columns) for tiles i = (g>>1) mod 2.  Warp 16 streams codebook tiles global->shared with
+// cp.async.bulk (TMA engine) through a ring of mbarrier-guarded stages, warp 17 issues the
+// MMAs.  The codebook is pre-arranged in global memory in exactly the shared-memory
+// core-matrix order (prepare_codebook_tc_kernel), so a tile is ONE contiguous bulk copy and
+// no tensor map is needed.
 #pragma once
 #include "vq_scores.cuh"
 
 namespace b200vq {
 
 constexpr int kTcRows = 128;       // token rows per CTA (UMMA M)
-constexpr int kTcCodes = 128;      // codes per tile (UMMA N)
-constexpr int kTcBufs = 4;         // TMEM accumulator buffers (4 x 128 columns), one per epilogue group
+constexpr int kTcCodes = 256;      // codes per tile (UMMA N)
+constexpr int kTcBufs = 2;         // TMEM accumulator buffers (2 x 256 columns)
 constexpr int kTcStages = 4;       // codebook tiles in flight
-constexpr int kTcEpiWarps = 4 * kTcBufs;
-constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);  // 16 epilogue warps + producer + MMA issuer
+constexpr int kTcEpiWarps = 16;    // 4 epilogue groups: group g drains columns [128*(g&1), +128) of buffer g>>1
+constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);  // + producer + MMA issuer
 constexpr float kTcMargin = 4e-5f; // ambiguity window on approximate scores (see header)
 
-// contraction length of the split operands, padded to the UMMA K of 16
-__host__ __device__ constexpr int tc_kc(int D) { return (3 * D + 15) / 16 * 16; }
-__host__ __device__ constexpr size_t tc_tile_bytes(int D) { return static_cast<size_t>(kTcCodes) * tc_kc(D) * 2; }
+// Split operands.  With P = D/8 16-byte chunks per part, the contraction runs over the virtual
+// chunk sequence   A: zh[0..P) zh[0..P) zl[0..P) (0)     B: eh[0..P) el[0..P) eh[0..P) (x)
+// two chunks (one K=16 MMA) at a time.  B is stored ONCE as eh[0..P) el[0..P): the third part
+// re-reads eh through its own descriptor, and because 2P is even no MMA straddles the wrap.
+__host__ __device__ constexpr int tc_parts(int D) { return D / 8; }
+__host__ __device__ constexpr int tc_slabs(int D) { return (3 * tc_parts(D) + 1) / 2; }           // MMAs per tile
+__host__ __device__ constexpr int tc_a_chunks(int D) { return 2 * tc_slabs(D); }
+__host__ __device__ constexpr int tc_b_chunks(int D) { return 2 * tc_parts(D); }
+__host__ __device__ constexpr size_t tc_tile_bytes(int D) { return static_cast<size_t>(kTcCodes) * tc_b_chunks(D) * 16; }
 __host__ __device__ constexpr bool tc_dim_ok(int D) { return D == 8 || D == 16 || D == 24 || D == 32; }
+// first B chunk of MMA j (the second is the next one)
+__host__ __device__ constexpr int tc_b_chunk_of_slab(int D, int j) { return (2 * j) % (2 * tc_parts(D)); }
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -128,43 +137,59 @@ __device__ __forceinline__ void split_bf16(float v, uint16_t& hi, uint16_t& lo) 
     hi = __bfloat16_as_ushort(h);
     lo = __bfloat16_as_ushort(l);
 }
-// element kk of the tripled contraction: A side [z_hi | z_hi | z_lo | 0], B side [e_hi | e_lo | e_hi | 0]
-template <int D, bool IS_A>
-__device__ __forceinline__ uint16_t split_elem(const uint16_t (&hi)[D], const uint16_t (&lo)[D], int kk) {
-    if (kk < D) return hi[kk];
-    if (kk < 2 * D) return IS_A ? hi[kk - D] : lo[kk - D];
-    if (kk < 3 * D) return IS_A ? lo[kk - 2 * D] : hi[kk - 2 * D];
-    return 0;
+// 16-byte chunk c of the A operand's virtual sequence zh[0..P) zh[0..P) zl[0..P) (0)
+template <int D>
+__device__ __forceinline__ uint4 a_chunk(const uint16_t (&hi)[D], const uint16_t (&lo)[D], int c) {
+    constexpr int P = tc_parts(D);
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+    if (c < 3 * P) {
+        const int part = c / P, q = c % P;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const uint32_t a = part < 2 ? hi[q * 8 + 2 * e] : lo[q * 8 + 2 * e];
+            const uint32_t b = part < 2 ? hi[q * 8 + 2 * e + 1] : lo[q * 8 + 2 * e + 1];
+            w[e] = a | (b << 16);
+        }
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // =======================================================================================
-// Codebook image for the tensor-core path: for tile t, 16-byte K-chunk c, code r of the tile,
-// the 8 bf16 values live at ((t * (Kc/8) + c) * 128 + r) * 16 bytes -- the shared-memory
-// core-matrix order, so a tile is one contiguous bulk copy.  One thread per code.
+// Codebook image for the tensor-core path: for tile t, chunk c in [0, 2P) (eh chunks then el
+// chunks), code r of the tile, the 8 bf16 values live at ((t * 2P + c) * 256 + r) * 16 bytes
+// -- the shared-memory core-matrix order, so a tile is one contiguous bulk copy.  One thread
+// per code.  flags[0] is set when a code row is not unit-norm (a zero row after
+// normalisation): argmin-distance then differs from argmax-cosine and the deterministic
+// tensor-core pass re-scores every row exactly.
 // =======================================================================================
 template <int D>
 __global__ void __launch_bounds__(kTcCodes) prepare_codebook_tc_kernel(const float* __restrict__ emb, int64_t K,
-                                                                  uint4* __restrict__ image) {
-    constexpr int KC = tc_kc(D);
+                                                                       uint4* __restrict__ image,
+                                                                       unsigned int* __restrict__ flags) {
+    constexpr int P = tc_parts(D);
     const int64_t code = static_cast<int64_t>(blockIdx.x) * kTcCodes + threadIdx.x;  // padded to whole tiles
     const int64_t tile = blockIdx.x;
     const int r = threadIdx.x;
     uint16_t hi[D], lo[D];
+    float e2 = 0.f;
 #pragma unroll
     for (int d = 0; d < D; ++d) {
         const float v = code < K ? emb[code * D + d] : 0.f;
+        e2 = fmaf(v, v, e2);
         split_bf16(v, hi[d], lo[d]);
     }
+    if (code < K && !(fabsf(e2 - 1.0f) <= 1e-5f)) atomicOr(flags, 1u);
 #pragma unroll
-    for (int c = 0; c < KC / 8; ++c) {
+    for (int c = 0; c < 2 * P; ++c) {
         uint32_t w[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            const uint32_t a = split_elem<D, false>(hi, lo, c * 8 + 2 * e);
-            const uint32_t b = split_elem<D, false>(hi, lo, c * 8 + 2 * e + 1);
+            const int d = (c % P) * 8 + 2 * e;
+            const uint32_t a = c < P ? hi[d] : lo[d];
+            const uint32_t b = c < P ? hi[d + 1] : lo[d + 1];
             w[e] = a | (b << 16);
         }
-        image[(tile * (KC / 8) + c) * kTcCodes + r] = make_uint4(w[0], w[1], w[2], w[3]);
+        image[(tile * (2 * P) + c) * kTcCodes + r] = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 

@@ -59,6 +59,7 @@ struct TcParams {
     int64_t row_offset;
     unsigned long long* keys; // (N) merged with atomicMax
     float* second;            // (N) deterministic modes: runner-up approximate score (orderable bits, atomicMax)
+    int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies
 };
 
 // per-warp queue + per-row state shared by the epilogue warps of a CTA
@@ -166,14 +167,14 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // =======================================================================================
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
-    return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_kc(D) * 2 + kTcStages * tc_tile_bytes(D) +
+    return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_a_chunks(D) * 16 + kTcStages * tc_tile_bytes(D) +
            kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + kTcRows * 4 + 256;
 }
 
 template <int D, typename T, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams p) {
-    constexpr int KC = tc_kc(D);
-    constexpr uint32_t A_BYTES = kTcRows * KC * 2;
+    constexpr int SLABS = tc_slabs(D);
+    constexpr uint32_t A_BYTES = kTcRows * tc_a_chunks(D) * 16;
     constexpr uint32_t B_BYTES = static_cast<uint32_t>(tc_tile_bytes(D));
     constexpr uint32_t A_LBO = kTcRows * 16, B_LBO = kTcCodes * 16, SBO = 128;
     constexpr bool SAMPLE = MODE == B200VQ_MODE_SAMPLE;
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     float* s_queue = reinterpret_cast<float*>(sB + kTcStages * B_BYTES);
     unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_queue + kTcEpiWarps * kQueueSlots * kQueueWords);
     uint32_t* s_second = reinterpret_cast<uint32_t*>(s_key + kTcRows);
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_second + kTcRows);  // full[S], empty[S], tfull[4], tempty[4]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_second + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 2 * kTcBufs);
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -213,20 +214,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
 #pragma unroll
         for (int d = 0; d < D; ++d) split_bf16(zn[d], hi[d], lo[d]);
 #pragma unroll
-        for (int c = 0; c < KC / 8; ++c) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                w[e] = static_cast<uint32_t>(split_elem<D, true>(hi, lo, c * 8 + 2 * e)) |
-                       (static_cast<uint32_t>(split_elem<D, true>(hi, lo, c * 8 + 2 * e + 1)) << 16);
-            *reinterpret_cast<uint4*>(sA + c * A_LBO + threadIdx.x * 16) = make_uint4(w[0], w[1], w[2], w[3]);
-        }
+        for (int c = 0; c < tc_a_chunks(D); ++c)
+            *reinterpret_cast<uint4*>(sA + c * A_LBO + threadIdx.x * 16) = a_chunk<D>(hi, lo, c);
         s_key[threadIdx.x] = make_key(-INFINITY, first_code);
         s_second[threadIdx.x] = kOrdNegInf;
     } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTcStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-            for (int b = 0; b < kTcBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 128); }
+            for (int b = 0; b < kTcBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 256); }
             fence_barrier_init();
         }
     } else if (warp == kTcEpiWarps + 1) {
@@ -245,6 +240,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             for (int i = 0; i < ntiles; ++i) {
                 const int s = i % kTcStages;
                 mbar_wait(bar_empty + 8 * s, ((i / kTcStages) & 1) ^ 1);
+                if (p.debug & 4) { mbar_arrive(bar_full + 8 * s); continue; }
                 mbar_expect_tx(bar_full + 8 * s, B_BYTES);
                 bulk_g2s(smem_u32(sB + s * B_BYTES), src + static_cast<size_t>(i) * B_BYTES, B_BYTES, bar_full + 8 * s);
             }
@@ -260,17 +256,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 tc_fence_after();
                 const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + s * B_BYTES);
 #pragma unroll
-                for (int k = 0; k < KC / 16; ++k) {
+                for (int k = 0; k < SLABS; ++k) {
+                    if (p.debug & 1) break;
                     umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
-                              umma_desc(b0 + k * 2 * B_LBO, B_LBO, SBO), idesc, k > 0);
+                              umma_desc(b0 + tc_b_chunk_of_slab(D, k) * B_LBO, B_LBO, SBO), idesc, k > 0);
                 }
                 umma_commit(bar_empty + 8 * s);     // stage reusable once these MMAs have read it
-                umma_commit(bar_tfull + 8 * buf);   // accumulator buffer ready for its epilogue group
+                umma_commit(bar_tfull + 8 * buf);   // accumulator buffer ready for its epilogue groups
             }
         }
     } else {
-        // ===== epilogue groups: group g = warps 4g..4g+3 drains TMEM buffer g ================================
-        const int grp = warp >> 2;
+        // ===== epilogue groups: group g = warps 4g..4g+3, columns [128*(g&1), +128) of buffer g>>1 ==========
+        const int grp = warp >> 2, buf = grp >> 1, half = grp & 1;
         Epi c;
         c.queue = s_queue + warp * kQueueSlots * kQueueWords;
         c.s_key = s_key;
@@ -284,13 +281,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         c.seed = p.seed;
         c.offset = p.offset;
         c.k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
-        const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + grp * kTcCodes;
+        const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
         const float tl2e = p.t_inv * kLog2e;
         uint32_t v[32];
-        for (int i = grp; i < ntiles; i += kTcBufs) {
-            const int64_t tile_code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes;  // index within the image
-            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + tile_code0) >> 3);  // multiple of 16
-            const int valid = static_cast<int>(min(static_cast<int64_t>(kTcCodes), p.K - tile_code0));
+        for (int i = buf; i < ntiles; i += kTcBufs) {
+            const int64_t code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes + half * 128;  // index within the image
+            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);            // multiple of 16
+            const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
             uint32_t hi16[16];
             if (SAMPLE) {   // 16 random bits per group, two Philox calls per tile, before the accumulator is needed
                 const Philox4 r0 = group_head_words(group0 >> 3, c.grow0 + c.row_local, p.seed, p.offset);
@@ -298,15 +295,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
 #pragma unroll
                 for (int q = 0; q < 8; ++q) { hi16[q] = head_hi16(r0, q); hi16[8 + q] = head_hi16(r1, q); }
             }
-            mbar_wait(bar_tfull + 8 * grp, (i / kTcBufs) & 1);
+            mbar_wait(bar_tfull + 8 * buf, (i / kTcBufs) & 1);
             tc_fence_after();
+            if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
 #pragma unroll
-            for (int ch = 0; ch < kTcCodes / 32; ++ch) {
+            for (int ch = 0; ch < 4; ++ch) {
                 tmem_ld32(t_lane + ch * 32, v);
                 tmem_ld_wait32(v);
-                if (ch == kTcCodes / 32 - 1) {   // accumulator buffer is in registers: hand it back to the MMA warp
+                if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
                     tc_fence_before();
-                    mbar_arrive(bar_tempty + 8 * grp);
+                    mbar_arrive(bar_tempty + 8 * buf);
                 }
                 if ((ch + 1) * 32 > valid) {
 #pragma unroll
@@ -350,16 +348,26 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     if (warp == kTcEpiWarps + 1) tmem_dealloc(tmem_base, 512);
 }
 
+// =======================================================================================
+// Exact re-scoring of the rows the tensor-core pass could not decide (runner-up within
+// kTcMargin of the best approximate score, or every row when the codebook has a non-unit
+// row and the mode ranks by distance).  Same fp32 arithmetic as scores_kernel, so the final
+// indices are bit-identical to the exact path.  Each CTA owns a contiguous range of rows,
+// collects the undecided ones 256 at a time and re-scans the codebook for each with all
+// 256 threads.
+// =======================================================================================
 template <int D, typename T, int MODE>
 __global__ void __launch_bounds__(256) resolve_kernel(const T* __restrict__ z, int64_t z_row_stride, int64_t N,
                                                       const float* __restrict__ emb, const float* __restrict__ e2,
                                                       int64_t K, int64_t k_offset, int l2norm,
                                                       unsigned long long* __restrict__ keys,
                                                       const float* __restrict__ second,
+                                                      const unsigned int* __restrict__ flags,
                                                       unsigned int* __restrict__ n_resolved) {
     __shared__ int s_list[256];
     __shared__ int s_count;
     __shared__ unsigned long long s_red[8];
+    const bool all_rows = MODE == B200VQ_MODE_ARGMIN_DIST && flags != nullptr && (*flags & 1u);
     const int64_t per_cta = (N + gridDim.x - 1) / gridDim.x;
     const int64_t r_begin = static_cast<int64_t>(blockIdx.x) * per_cta;
     const int64_t r_end = min(N, r_begin + per_cta);
@@ -371,7 +379,7 @@ __global__ void __launch_bounds__(256) resolve_kernel(const T* __restrict__ z, i
             const float best = key_value(keys[row]);
             const uint32_t so = reinterpret_cast<const unsigned int*>(second)[row];
             const float sec = so == 0u ? -INFINITY : __uint_as_float((so & 0x80000000u) ? (so ^ 0x80000000u) : ~so);
-            if (!(best - sec >= kTcMargin)) s_list[atomicAdd(&s_count, 1)] = threadIdx.x;
+            if (all_rows || !(best - sec >= kTcMargin)) s_list[atomicAdd(&s_count, 1)] = threadIdx.x;
         }
         __syncthreads();
         const int cnt = s_count;
@@ -382,6 +390,7 @@ __global__ void __launch_bounds__(256) resolve_kernel(const T* __restrict__ z, i
             load_normalised_row<D, T>(z + r * z_row_stride, l2norm, zn, z2, zlen);
             float best_v = -INFINITY;
             uint32_t best_k = static_cast<uint32_t>(k_offset);
+#pragma unroll 4
             for (int64_t k = threadIdx.x; k < K; k += 256) {
                 const float* e = emb + k * D;
                 float acc = 0.f;
