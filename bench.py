@@ -305,14 +305,17 @@ def run_b200(args):
         emb, e2, _ = VF.prepare_codebook(m.regularizer.embedding.weight, True)
         image = VF.prepare_codebook_tc(emb)
     keys = torch.zeros(N, dtype=torch.int64, device=dev)
-    second = torch.zeros(N, dtype=torch.float32, device=dev)
+    second = torch.zeros(2 * N + 4, dtype=torch.float32, device=dev)
     st = torch.cuda.current_stream().cuda_stream
 
     def scores_exact():
+        keys.zero_()
         _lib.check(lib.b200vq_scores_partial(z.data_ptr(), 0, D, N, D, emb.data_ptr(), e2.data_ptr(), K, 0, mode, 1,
                                              1.0 / CFG["T"], 1, 4, 0, keys.data_ptr(), st), "scores")
 
     def scores_tc():
+        keys.zero_()      # the step does the same resets (b200vq_forward zeroes its workspace)
+        second.zero_()
         _lib.check(lib.b200vq_scores_tc(z.data_ptr(), 0, D, N, D, image.data_ptr(), emb.data_ptr(), e2.data_ptr(), K, 0,
                                         mode, 1, 1.0 / CFG["T"], 1, 4, 0, keys.data_ptr(), second.data_ptr(), None, st),
                    "scores_tc")

@@ -109,17 +109,19 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
  *   b200vq_tc_supported   1 if (D, l2norm, mode) can take this path (D in {8,16,24,32}, l2norm)
  *   b200vq_tc_image_bytes size of the codebook image for K codes
  *   b200vq_prepare_codebook_tc  emb (K,D) fp32 normalised codebook -> image (16-byte aligned)
- *   second      (N) fp32 scratch, zeroed by the caller with keys (deterministic modes)
+ *   scratch     b200vq_tc_scratch_bytes(N) bytes, zeroed by the caller with keys (deterministic
+ *               modes): runner-up scores, then the list of undecided rows
  *   n_resolved  nullable device counter, += number of rows re-scored exactly
  *   k_offset    multiple of 256
  */
 int b200vq_tc_supported(int D, int l2norm, int mode);
 size_t b200vq_tc_image_bytes(int64_t K, int D);
+size_t b200vq_tc_scratch_bytes(int64_t N);
 int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, b200vq_stream_t stream);
 int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D,
                      const void* image, const float* emb, const float* e2, int64_t K, int64_t k_offset,
                      int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
-                     int64_t row_offset, uint64_t* keys, float* second, unsigned int* n_resolved,
+                     int64_t row_offset, uint64_t* keys, float* scratch, unsigned int* n_resolved,
                      b200vq_stream_t stream);
 
 /*

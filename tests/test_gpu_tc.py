@@ -30,7 +30,7 @@ def _scores(z, w, mode, tc, seed=7, offset=12, t_inv=1 / 0.03, row_offset=0):
     dt = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[z.dtype]
     if tc:
         image = VF.prepare_codebook_tc(emb)
-        second = torch.zeros(N, dtype=torch.float32, device=DEV)
+        second = torch.zeros(2 * N + 4, dtype=torch.float32, device=DEV)
         _lib.check(lib.b200vq_scores_tc(z.data_ptr(), dt, D, N, D, image.data_ptr(), emb.data_ptr(), e2.data_ptr(), K, 0,
                                         mode, 1, t_inv, seed, offset, row_offset, keys.data_ptr(), second.data_ptr(),
                                         nres.data_ptr(), _stream()), "scores_tc")

@@ -23,7 +23,7 @@ z = torch.randn(a.N, a.D, device=dev)
 w = torch.empty(a.K, a.D, device=dev); torch.nn.init.kaiming_uniform_(w)
 emb, e2, _ = VF.prepare_codebook(w, True)
 image = VF.prepare_codebook_tc(emb)
-ws = torch.zeros(a.N * 3 + 64, dtype=torch.int32, device=dev)  # keys (2 words/row) + second
+ws = torch.zeros(a.N * 4 + 64, dtype=torch.int32, device=dev)  # keys (2 words/row) + tc scratch
 keys_ptr, second_ptr = ws.data_ptr(), ws.data_ptr() + a.N * 8
 nres = torch.zeros(1, dtype=torch.int32, device=dev)
 st = torch.cuda.current_stream().cuda_stream

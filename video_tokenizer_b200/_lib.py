@@ -35,6 +35,7 @@ SIGNATURES = {
                              _vp, _vp, _vp, _i32, _i64, _f32, _f32, _vp, _vp]),
     "b200vq_tc_supported": (_i32, [_i32, _i32, _i32]),
     "b200vq_tc_image_bytes": (_sz, [_i64, _i32]),
+    "b200vq_tc_scratch_bytes": (_sz, [_i64]),
     "b200vq_prepare_codebook_tc": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "b200vq_scores_tc": (_i32, [_vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _f32, _u64, _u64,
                                 _i64, _vp, _vp, _vp, _vp]),

@@ -104,9 +104,9 @@ const char* b200vq_error_string(int code) {
 size_t b200vq_workspace_bytes(int64_t N, int D, int64_t K) {
     (void)D; (void)K;
     if (N < 0) return 0;
-    // [keys: N u64][scratch: sum + ticket, 2 doubles][runner-up scores: N f32][resolved-row counter]
+    // [keys: N u64][sum + ticket, 2 doubles][resolved-row counter][tensor-core scratch]
     return align_up(static_cast<size_t>(N) * sizeof(uint64_t)) + align_up(2 * sizeof(double)) +
-           align_up(static_cast<size_t>(N) * sizeof(float)) + align_up(sizeof(unsigned int));
+           align_up(sizeof(unsigned int)) + align_up(b200vq_tc_scratch_bytes(N));
 }
 
 int b200vq_prepare_codebook(const float* weight, int64_t K, int D, int l2norm, float* emb, float* e2,
@@ -183,6 +183,11 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
 }
 
 // ---- tensor-core path --------------------------------------------------------------------------
+size_t b200vq_tc_scratch_bytes(int64_t N) {
+    // [runner-up scores: N f32][undecided-row list: count + 3 pad, N u32]; the caller zeroes it
+    return N < 0 ? 0 : static_cast<size_t>(N) * 8 + 16;
+}
+
 int b200vq_tc_supported(int D, int l2norm, int mode) {
     return tc_dim_ok(D) && l2norm && valid_mode(mode) ? 1 : 0;
 }
@@ -215,14 +220,14 @@ int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, 
 
 int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const void* image,
                      const float* emb, const float* e2, int64_t K, int64_t k_offset, int mode, int l2norm,
-                     float t_inv, uint64_t seed, uint64_t offset, int64_t row_offset, uint64_t* keys, float* second,
+                     float t_inv, uint64_t seed, uint64_t offset, int64_t row_offset, uint64_t* keys, float* scratch,
                      unsigned int* n_resolved, b200vq_stream_t stream) {
     if (N < 0 || K <= 0 || k_offset < 0 || row_offset < 0 || !valid_dtype(z_dtype) || !valid_mode(mode)) return B200VQ_EINVAL;
     if (!tc_dim_ok(D)) return B200VQ_EDIM;
     if (!l2norm) return B200VQ_EINVAL;  // the error bound assumes unit vectors
     if (N == 0) return B200VQ_OK;
     if (!z || !image || !keys || z_row_stride < D) return B200VQ_EINVAL;
-    if (mode != B200VQ_MODE_SAMPLE && (!emb || !e2 || !second)) return B200VQ_EINVAL;
+    if (mode != B200VQ_MODE_SAMPLE && (!emb || !e2 || !scratch)) return B200VQ_EINVAL;
     if (k_offset & (kTcCodes - 1)) return B200VQ_EALIGN;
     if (k_offset + K > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -252,7 +257,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     prm.z = z; prm.z_row_stride = z_row_stride; prm.N = N; prm.image = static_cast<const uint4*>(image);
     prm.K = K; prm.k_offset = k_offset; prm.tiles_per_split = per; prm.l2norm = l2norm; prm.t_inv = t_inv;
     prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
-    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = second;
+    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = scratch;
     prm.debug = 0;
     if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
@@ -269,11 +274,16 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     // exact re-scoring of undecided rows (deterministic modes)
     const unsigned int* flags = reinterpret_cast<const unsigned int*>(
         static_cast<const char*>(image) + static_cast<size_t>(total_tiles) * tc_tile_bytes(D));
-    const unsigned rblocks = static_cast<unsigned>(std::min<int64_t>((N + 255) / 256, 4ll * sms));
     unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
-#define B200VQ_RESOLVE(DD, MM)                                                                                   \
-    resolve_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, N, emb, e2, K,    \
-                                                        k_offset, l2norm, k64, second, flags, n_resolved)
+    unsigned int* list = reinterpret_cast<unsigned int*>(scratch + N);
+    collect_undecided_kernel<<<static_cast<unsigned>((N + 255) / 256), 256, 0, st>>>(
+        k64, scratch, N, flags, mode == B200VQ_MODE_ARGMIN_DIST ? 1 : 0, list);
+    rc = launch_check();
+    if (rc) return rc;
+    const unsigned rblocks = static_cast<unsigned>(std::min<int64_t>(N, 8ll * sms));
+#define B200VQ_RESOLVE(DD, MM)                                                                                \
+    rescore_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, emb, e2, K,    \
+                                                        k_offset, l2norm, k64, list, n_resolved)
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
         if (mode == B200VQ_MODE_ARGMIN_DIST) {
             switch (D) {
@@ -345,8 +355,8 @@ int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, 
     if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
     if (image && b200vq_tc_supported(D, l2norm, mode)) {
         char* base = static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double));
-        float* second = reinterpret_cast<float*>(base);
-        unsigned int* n_resolved = reinterpret_cast<unsigned int*>(base + align_up(static_cast<size_t>(N) * sizeof(float)));
+        unsigned int* n_resolved = reinterpret_cast<unsigned int*>(base);
+        float* second = reinterpret_cast<float*>(base + align_up(sizeof(unsigned int)));
         rc = b200vq_scores_tc(z, z_dtype, z_row_stride, N, D, image, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
                               keys, second, n_resolved, stream);
     } else {

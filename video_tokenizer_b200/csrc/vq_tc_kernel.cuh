@@ -29,6 +29,21 @@ __device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
                  : "memory");
 }
 
+__device__ __forceinline__ void tmem_ld_wait64(uint32_t (&r)[64]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]),
+                   "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]),
+                   "+r"(r[30]), "+r"(r[31]), "+r"(r[32]), "+r"(r[33]), "+r"(r[34]), "+r"(r[35]), "+r"(r[36]),
+                   "+r"(r[37]), "+r"(r[38]), "+r"(r[39]), "+r"(r[40]), "+r"(r[41]), "+r"(r[42]), "+r"(r[43]),
+                   "+r"(r[44]), "+r"(r[45]), "+r"(r[46]), "+r"(r[47]), "+r"(r[48]), "+r"(r[49]), "+r"(r[50]),
+                   "+r"(r[51]), "+r"(r[52]), "+r"(r[53]), "+r"(r[54]), "+r"(r[55]), "+r"(r[56]), "+r"(r[57]),
+                   "+r"(r[58]), "+r"(r[59]), "+r"(r[60]), "+r"(r[61]), "+r"(r[62]), "+r"(r[63])
+                 :
+                 : "memory");
+}
+
 __device__ __forceinline__ float max8(const uint32_t* v) {
     const float a = fmaxf(fmaxf(__uint_as_float(v[0]), __uint_as_float(v[1])), __uint_as_float(v[2]));
     const float b = fmaxf(fmaxf(__uint_as_float(v[3]), __uint_as_float(v[4])), __uint_as_float(v[5]));
@@ -59,7 +74,7 @@ struct TcParams {
     int64_t row_offset;
     unsigned long long* keys; // (N) merged with atomicMax
     float* second;            // (N) deterministic modes: runner-up approximate score (orderable bits, atomicMax)
-    int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies
+    int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies, 64 = no events
 };
 
 // per-warp queue + per-row state shared by the epilogue warps of a CTA
@@ -67,6 +82,7 @@ struct Epi {
     float* queue;                 // this warp's ring
     unsigned long long* s_key;    // (128) per-row best (value, code)
     uint32_t* s_second;           // (128) per-row runner-up value, orderable bits (deterministic)
+    uint32_t* s_thr;              // (128) per-row largest group maximum pushed so far, orderable bits (deterministic)
     uint32_t qhead, qtail;        // warp-uniform
     uint32_t row_local, lane;
     float thr;                    // lane's row: det = best - margin ; sample = 19.02 - vstar*log2(e)
@@ -136,15 +152,19 @@ __device__ __forceinline__ void epi_flush(Epi& c, uint32_t n) {
         c.thr = fmaf(key_value(c.s_key[c.row_local]), -kLog2e, 19.02f);
     } else {
         det_flush(c.queue, c.qhead, n, c.lane, c.s_key, c.s_second);
-        c.thr = key_value(c.s_key[c.row_local]) - kTcMargin;
     }
     c.qhead += n;
 }
 
 // push the groups flagged in this warp (ballot b) and drain the queue when 32 are waiting
 template <bool SAMPLE>
-__device__ __forceinline__ void epi_push(Epi& c, uint32_t b, bool ev, const uint32_t* v8, uint32_t group, uint32_t hi16) {
+__device__ __forceinline__ void epi_push(Epi& c, uint32_t b, bool ev, const uint32_t* v8, uint32_t group, uint32_t hi16,
+                                         float m) {
     if (ev) {
+        if (!SAMPLE) {   // the group maximum is a lower bound of the row's best: later groups must beat it
+            c.thr = fmaxf(c.thr, m - kTcMargin);
+            atomicMax(c.s_thr + c.row_local, orderable(m));
+        }
         const uint32_t slot = (c.qtail + __popc(b & ((1u << c.lane) - 1u))) & (kQueueSlots - 1);
         float* e = c.queue + slot * kQueueWords;
         *reinterpret_cast<uint4*>(e) = make_uint4(v8[0], v8[1], v8[2], v8[3]);
@@ -168,7 +188,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
     return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_a_chunks(D) * 16 + kTcStages * tc_tile_bytes(D) +
-           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + kTcRows * 4 + 256;
+           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + 2 * kTcRows * 4 + 256;
 }
 
 template <int D, typename T, int MODE>
@@ -186,7 +206,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     float* s_queue = reinterpret_cast<float*>(sB + kTcStages * B_BYTES);
     unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_queue + kTcEpiWarps * kQueueSlots * kQueueWords);
     uint32_t* s_second = reinterpret_cast<uint32_t*>(s_key + kTcRows);
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_second + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
+    uint32_t* s_thr = s_second + kTcRows;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_thr + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 2 * kTcBufs);
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -218,6 +239,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             *reinterpret_cast<uint4*>(sA + c * A_LBO + threadIdx.x * 16) = a_chunk<D>(hi, lo, c);
         s_key[threadIdx.x] = make_key(-INFINITY, first_code);
         s_second[threadIdx.x] = kOrdNegInf;
+        s_thr[threadIdx.x] = kOrdNegInf;
     } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTcStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -245,24 +267,26 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 bulk_g2s(smem_u32(sB + s * B_BYTES), src + static_cast<size_t>(i) * B_BYTES, B_BYTES, bar_full + 8 * s);
             }
         }
-    } else if (warp == kTcEpiWarps + 1) {
-        // ===== MMA issuer =====================================================================================
+    } else if (warp >= kTcEpiWarps + 1) {
+        // ===== MMA issuers: warp 17 issues the tiles of buffer 0, warp 18 those of buffer 1 ===============
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTcCodes);
-            for (int i = 0; i < ntiles; ++i) {
-                const int buf = i % kTcBufs, s = i % kTcStages;
+            const int buf = warp - (kTcEpiWarps + 1);
+            const uint32_t a0 = smem_u32(sA);
+            for (int i = buf; i < ntiles; i += kTcBufs) {
+                const int s = i % kTcStages;
                 mbar_wait(bar_tempty + 8 * buf, ((i / kTcBufs) & 1) ^ 1);
                 mbar_wait(bar_full + 8 * s, (i / kTcStages) & 1);
                 tc_fence_after();
-                const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB + s * B_BYTES);
+                const uint32_t b0 = smem_u32(sB + s * B_BYTES);
 #pragma unroll
                 for (int k = 0; k < SLABS; ++k) {
                     if (p.debug & 1) break;
                     umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
                               umma_desc(b0 + tc_b_chunk_of_slab(D, k) * B_LBO, B_LBO, SBO), idesc, k > 0);
                 }
-                umma_commit(bar_empty + 8 * s);     // stage reusable once these MMAs have read it
-                umma_commit(bar_tfull + 8 * buf);   // accumulator buffer ready for its epilogue groups
+                // one commit per tile: the epilogue group that sees it also frees the codebook stage
+                umma_commit(bar_tfull + 8 * buf);
             }
         }
     } else {
@@ -272,6 +296,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         c.queue = s_queue + warp * kQueueSlots * kQueueWords;
         c.s_key = s_key;
         c.s_second = s_second;
+        c.s_thr = s_thr;
         c.qhead = c.qtail = 0;
         c.row_local = 32 * (warp & 3) + lane;
         c.lane = lane;
@@ -288,19 +313,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             const int64_t code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes + half * 128;  // index within the image
             const uint32_t group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);            // multiple of 16
             const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
-            uint32_t hi16[16];
+            Philox4 r0, r1;
             if (SAMPLE) {   // 16 random bits per group, two Philox calls per tile, before the accumulator is needed
-                const Philox4 r0 = group_head_words(group0 >> 3, c.grow0 + c.row_local, p.seed, p.offset);
-                const Philox4 r1 = group_head_words((group0 >> 3) + 1, c.grow0 + c.row_local, p.seed, p.offset);
-#pragma unroll
-                for (int q = 0; q < 8; ++q) { hi16[q] = head_hi16(r0, q); hi16[8 + q] = head_hi16(r1, q); }
+                r0 = group_head_words(group0 >> 3, c.grow0 + c.row_local, p.seed, p.offset);
+                r1 = group_head_words((group0 >> 3) + 1, c.grow0 + c.row_local, p.seed, p.offset);
+                c.thr = fmaf(key_value(s_key[c.row_local]), -kLog2e, 19.02f);      // other groups' progress
+            } else {
+                c.thr = fmaxf(c.thr, ord_value(s_thr[c.row_local]) - kTcMargin);
             }
             mbar_wait(bar_tfull + 8 * buf, (i / kTcBufs) & 1);
             tc_fence_after();
+            if (half == 0 && (warp & 3) == 0 && lane == 0) mbar_arrive(bar_empty + 8 * (i % kTcStages));  // MMAs have read the stage
             if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
 #pragma unroll
             for (int ch = 0; ch < 4; ++ch) {
                 tmem_ld32(t_lane + ch * 32, v);
+                if (SAMPLE && ch > 0) c.thr = fmaf(key_value(s_key[c.row_local]), -kLog2e, 19.02f);
                 tmem_ld_wait32(v);
                 if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
                     tc_fence_before();
@@ -310,18 +338,34 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
 #pragma unroll
                     for (int j = 0; j < 32; ++j) if (ch * 32 + j >= valid) v[j] = 0xFF800000u;
                 }
+                // 4 groups: all maxima and tests first (independent), one vote for the rare path
+                float m[4];
+                uint32_t evmask = 0;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    const float m = max8(&v[8 * g]);
+                    m[g] = max8(&v[8 * g]);
                     bool ev;
                     if (SAMPLE) {
-                        const float fh = __uint_as_float(0x4B000000u | hi16[4 * ch + g]) - 8388608.0f;
-                        ev = fh < ex2_approx(fmaf(m, tl2e, c.thr));
+                        const uint32_t h = head_hi16(ch < 2 ? r0 : r1, 4 * (ch & 1) + g);
+                        const float fh = __uint_as_float(0x4B000000u | h) - 8388608.0f;
+                        ev = fh < ex2_approx(fmaf(m[g], tl2e, c.thr));
                     } else {
-                        ev = m > c.thr;
+                        ev = m[g] > c.thr;
                     }
-                    const uint32_t b = __ballot_sync(0xffffffffu, ev);
-                    if (b) epi_push<SAMPLE>(c, b, ev, &v[8 * g], group0 + 4 * ch + g, SAMPLE ? hi16[4 * ch + g] : 0u);
+                    evmask |= ev ? (1u << g) : 0u;
+                }
+                const uint32_t um = __reduce_or_sync(0xffffffffu, evmask);
+                if (um != 0u && !(p.debug & 64)) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        if (um & (1u << g)) {
+                            // re-test against the threshold the lane may have raised while pushing earlier groups
+                            const bool ev = ((evmask >> g) & 1u) && (SAMPLE || m[g] > c.thr);
+                            const uint32_t b = __ballot_sync(0xffffffffu, ev);
+                            if (b) epi_push<SAMPLE>(c, b, ev, &v[8 * g], group0 + 4 * ch + g,
+                                                    SAMPLE ? head_hi16(ch < 2 ? r0 : r1, 4 * (ch & 1) + g) : 0u, m[g]);
+                        }
+                    }
                 }
             }
         }
@@ -351,77 +395,79 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
 // =======================================================================================
 // Exact re-scoring of the rows the tensor-core pass could not decide (runner-up within
 // kTcMargin of the best approximate score, or every row when the codebook has a non-unit
-// row and the mode ranks by distance).  Same fp32 arithmetic as scores_kernel, so the final
-// indices are bit-identical to the exact path.  Each CTA owns a contiguous range of rows,
-// collects the undecided ones 256 at a time and re-scans the codebook for each with all
-// 256 threads.
+// row and the mode ranks by distance).  collect_undecided_kernel compacts their row ids,
+// rescore_kernel re-scans the codebook for one listed row per CTA iteration with the same
+// fp32 arithmetic as scores_kernel, so the final indices are bit-identical to the exact path.
+// list[0] = count, list[4 ..] = row ids.
 // =======================================================================================
+__global__ void __launch_bounds__(256) collect_undecided_kernel(const unsigned long long* __restrict__ keys,
+                                                                const float* __restrict__ second, int64_t N,
+                                                                const unsigned int* __restrict__ flags, int dist_mode,
+                                                                unsigned int* __restrict__ list) {
+    const bool all_rows = dist_mode && flags != nullptr && (*flags & 1u);
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;
+    bool take = false;
+    if (row < N) {
+        const float best = key_value(keys[row]);
+        const uint32_t so = reinterpret_cast<const unsigned int*>(second)[row];
+        const float sec = so == 0u ? -INFINITY : ord_value(so);
+        take = all_rows || !(best - sec >= kTcMargin);
+    }
+    const uint32_t b = __ballot_sync(0xffffffffu, take);
+    if (b) {
+        uint32_t base = 0;
+        if ((threadIdx.x & 31) == 0) base = atomicAdd(list, static_cast<unsigned int>(__popc(b)));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (take) list[4 + base + __popc(b & ((1u << (threadIdx.x & 31)) - 1u))] = static_cast<unsigned int>(row);
+    }
+}
+
 template <int D, typename T, int MODE>
-__global__ void __launch_bounds__(256) resolve_kernel(const T* __restrict__ z, int64_t z_row_stride, int64_t N,
+__global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ z, int64_t z_row_stride,
                                                       const float* __restrict__ emb, const float* __restrict__ e2,
                                                       int64_t K, int64_t k_offset, int l2norm,
                                                       unsigned long long* __restrict__ keys,
-                                                      const float* __restrict__ second,
-                                                      const unsigned int* __restrict__ flags,
+                                                      const unsigned int* __restrict__ list,
                                                       unsigned int* __restrict__ n_resolved) {
-    __shared__ int s_list[256];
-    __shared__ int s_count;
     __shared__ unsigned long long s_red[8];
-    const bool all_rows = MODE == B200VQ_MODE_ARGMIN_DIST && flags != nullptr && (*flags & 1u);
-    const int64_t per_cta = (N + gridDim.x - 1) / gridDim.x;
-    const int64_t r_begin = static_cast<int64_t>(blockIdx.x) * per_cta;
-    const int64_t r_end = min(N, r_begin + per_cta);
-    for (int64_t base = r_begin; base < r_end; base += 256) {
-        if (threadIdx.x == 0) s_count = 0;
-        __syncthreads();
-        const int64_t row = base + threadIdx.x;
-        if (row < r_end) {
-            const float best = key_value(keys[row]);
-            const uint32_t so = reinterpret_cast<const unsigned int*>(second)[row];
-            const float sec = so == 0u ? -INFINITY : __uint_as_float((so & 0x80000000u) ? (so ^ 0x80000000u) : ~so);
-            if (all_rows || !(best - sec >= kTcMargin)) s_list[atomicAdd(&s_count, 1)] = threadIdx.x;
-        }
-        __syncthreads();
-        const int cnt = s_count;
-        for (int i = 0; i < cnt; ++i) {
-            const int64_t r = base + s_list[i];
-            float zn[D];
-            float z2, zlen;
-            load_normalised_row<D, T>(z + r * z_row_stride, l2norm, zn, z2, zlen);
-            float best_v = -INFINITY;
-            uint32_t best_k = static_cast<uint32_t>(k_offset);
+    const unsigned int count = list[0];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_resolved) atomicAdd(n_resolved, count);
+    for (unsigned int it = blockIdx.x; it < count; it += gridDim.x) {
+        const int64_t r = list[4 + it];
+        float zn[D];
+        float z2, zlen;
+        load_normalised_row<D, T>(z + r * z_row_stride, l2norm, zn, z2, zlen);
+        float best_v = -INFINITY;
+        uint32_t best_k = static_cast<uint32_t>(k_offset);
 #pragma unroll 4
-            for (int64_t k = threadIdx.x; k < K; k += 256) {
-                const float* e = emb + k * D;
-                float acc = 0.f;
+        for (int64_t k = threadIdx.x; k < K; k += 256) {
+            const float* e = emb + k * D;
+            float acc = 0.f;
 #pragma unroll
-                for (int d = 0; d < D; d += 4) {
-                    const float4 ev = __ldg(reinterpret_cast<const float4*>(e + d));
-                    acc = fmaf(zn[d + 0], ev.x, acc);
-                    acc = fmaf(zn[d + 1], ev.y, acc);
-                    acc = fmaf(zn[d + 2], ev.z, acc);
-                    acc = fmaf(zn[d + 3], ev.w, acc);
-                }
-                const float v = rank_value<MODE>(acc, z2, __ldg(e2 + k), 1.0f, 0.f);
-                if (v > best_v) { best_v = v; best_k = static_cast<uint32_t>(k_offset + k); }
+            for (int d = 0; d < D; d += 4) {
+                const float4 ev = __ldg(reinterpret_cast<const float4*>(e + d));
+                acc = fmaf(zn[d + 0], ev.x, acc);
+                acc = fmaf(zn[d + 1], ev.y, acc);
+                acc = fmaf(zn[d + 2], ev.z, acc);
+                acc = fmaf(zn[d + 3], ev.w, acc);
             }
-            unsigned long long key = make_key(best_v, best_k);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
-                key = other > key ? other : key;
-            }
-            if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = key;
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                unsigned long long m = s_red[0];
-#pragma unroll
-                for (int w = 1; w < 8; ++w) m = s_red[w] > m ? s_red[w] : m;
-                keys[r] = m;
-            }
-            __syncthreads();
+            const float v = rank_value<MODE>(acc, z2, __ldg(e2 + k), 1.0f, 0.f);
+            if (v > best_v) { best_v = v; best_k = static_cast<uint32_t>(k_offset + k); }
         }
-        if (threadIdx.x == 0 && cnt && n_resolved) atomicAdd(n_resolved, static_cast<unsigned int>(cnt));
+        unsigned long long key = make_key(best_v, best_k);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+            key = other > key ? other : key;
+        }
+        if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = key;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long m = s_red[0];
+#pragma unroll
+            for (int w = 1; w < 8; ++w) m = s_red[w] > m ? s_red[w] : m;
+            keys[r] = m;
+        }
         __syncthreads();
     }
 }
