@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 101
+#define B200VQ_VERSION 102
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -217,6 +217,32 @@ int b200vq_usage_stats(const int32_t* hist_first, const int32_t* hist_batch, int
  */
 int b200vq_gather_owned(const uint64_t* keys, int64_t N, const float* emb_local, int64_t K_local,
                         int64_t k_offset, int D, float* out, b200vq_stream_t stream);
+
+/*
+ * The Bottleneck's two skinny linears and their backward (bottleneck.py:109-110 in_linear C->D,
+ * out_linear D->C; :140-142 project_in, :162-164 project_out), fp32 in / fp32 out, D in
+ * {8,16,24,32}, C a multiple of 16.  HBM-streaming kernels: every activation byte is touched
+ * once, the weight matrix sits in shared memory.
+ *   b200vq_linear_supported  1 if (C, D) can take these kernels (else use the framework's GEMM)
+ *   b200vq_linear_in    y (N,D) = x (N,C; row stride ldx) w^T + bias, w (D,C); 3xTF32 (fp32-class
+ *                       accuracy: y decides the code indices).  Also grad of out_linear's input
+ *                       (x = grad_output, w = out_linear.weight^T).
+ *   b200vq_linear_out   y (N,C; row stride ldy) = a (N,D) w'^T + bias (nullable); w' is (C,D)
+ *                       when w_is_dc == 0 (out_linear.weight) or (D,C) when w_is_dc == 1
+ *                       (in_linear.weight: grad_x = grad_z W_in).  TF32, fp32 accumulate.
+ *   b200vq_weight_grad  dw = x^T y  (x (N,C; ldx), y (N,D)), written as (C,D) or, dw_is_dc == 1,
+ *                       (D,C); colsum (C, nullable) = column sums of x (bias grad).  Outputs are
+ *                       zeroed inside; accumulation across CTAs uses fp32 atomics.
+ *   b200vq_colsum       out (D) = column sums of y (N,D), D <= 32 (in_linear.bias.grad)
+ */
+int b200vq_linear_supported(int C, int D);
+int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D,
+                     float* y, b200vq_stream_t stream);
+int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C,
+                      float* y, int64_t ldy, b200vq_stream_t stream);
+int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
+                       int dw_is_dc, float* colsum, b200vq_stream_t stream);
+int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream);
 
 #ifdef __cplusplus
 }

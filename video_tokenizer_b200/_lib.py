@@ -46,6 +46,11 @@ SIGNATURES = {
     "b200vq_codebook_backward": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "b200vq_decode": (_i32, [_vp, _i64, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "b200vq_usage_stats": (_i32, [_vp, _vp, _i64, _vp, _vp]),
+    "b200vq_linear_supported": (_i32, [_i32, _i32]),
+    "b200vq_linear_in": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _i32, _vp, _vp]),
+    "b200vq_linear_out": (_i32, [_vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp, _i64, _vp]),
+    "b200vq_weight_grad": (_i32, [_vp, _i64, _vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp]),
+    "b200vq_colsum": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "b200vq_gather_owned": (_i32, [_vp, _i64, _vp, _i64, _i64, _i32, _vp, _vp]),
 }
 
@@ -80,7 +85,7 @@ def load(build_if_missing: bool = True):
             except AttributeError as e:
                 raise B200VQError(f"{path} does not export {name}") from e
             fn.restype, fn.argtypes = res, args
-        if lib.b200vq_version() < 101:
+        if lib.b200vq_version() < 102:
             raise B200VQError("libb200vq.so is older than this Python package")
         _lib = lib
         return lib

@@ -230,7 +230,7 @@ class Bottleneck(nn.Module):
 
     def project_in(self, x):
         assert len(x.shape) == 3, "Input shape must be (batch, n_tokens, e_dim)"
-        z = self.in_linear(x)
+        z = VF.linear_in(x, self.in_linear.weight, self.in_linear.bias)
         if self.norm is not None:
             with torch.autocast(device_type="cuda", enabled=False):
                 z = z.float()
@@ -245,7 +245,7 @@ class Bottleneck(nn.Module):
         return z
 
     def project_out(self, z_cat):
-        return self.out_linear(z_cat)
+        return VF.linear_out(z_cat, self.out_linear.weight, self.out_linear.bias)
 
     def decode(self, bottleneck_rep):
         regularized_z = self.regularizer.decode(bottleneck_rep)

@@ -1,6 +1,7 @@
 // b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
 #include "vq_generic.cuh"
 #include "vq_tc_kernel.cuh"
+#include "vq_linear.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -432,6 +433,112 @@ int b200vq_gather_owned(const uint64_t* keys, int64_t N, const float* emb_local,
     const int64_t total = N * D;
     gather_owned_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<const unsigned long long*>(keys), N, emb_local, K_local, k_offset, D, out);
+    return launch_check();
+}
+
+}  // extern "C"
+
+// ---- the Bottleneck's skinny linears ----------------------------------------------------------------
+namespace {
+inline bool lin_dim_ok(int D) { return D == 8 || D == 16 || D == 24 || D == 32; }
+template <typename K>
+inline int set_smem(K kernel, size_t bytes) {
+    if (bytes <= 48 * 1024) return B200VQ_OK;
+    return cuda_check(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+}
+}  // namespace
+
+extern "C" {
+
+int b200vq_linear_supported(int C, int D) {
+    if (!lin_dim_ok(D) || C < 16 || (C % 16) != 0) return 0;
+    const size_t in_smem = static_cast<size_t>(D) * (C + 16) * 4, out_smem = static_cast<size_t>(C) * (D + 4) * 4;
+    return in_smem <= 200 * 1024 && out_smem <= 200 * 1024 ? 1 : 0;
+}
+
+int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D, float* y,
+                     b200vq_stream_t stream) {
+    if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
+    if (N == 0) return B200VQ_OK;
+    if (!x || !w || !y || ldx < C) return B200VQ_EINVAL;
+    if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w) & 15) ||
+        (reinterpret_cast<uintptr_t>(y) & 7))
+        return B200VQ_EALIGN;
+    const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
+    const unsigned blocks = static_cast<unsigned>((N + kLinRows - 1) / kLinRows);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = B200VQ_OK;
+#define B200VQ_LIN_IN(DD)                                                            \
+    if ((rc = set_smem(linear_in_kernel<DD>, smem))) return rc;                      \
+    linear_in_kernel<DD><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, bias, y)
+    switch (D) {
+        case 8: B200VQ_LIN_IN(8); break;
+        case 16: B200VQ_LIN_IN(16); break;
+        case 24: B200VQ_LIN_IN(24); break;
+        default: B200VQ_LIN_IN(32); break;
+    }
+#undef B200VQ_LIN_IN
+    return launch_check();
+}
+
+int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
+                      int64_t ldy, b200vq_stream_t stream) {
+    if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
+    if (N == 0) return B200VQ_OK;
+    if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
+    if ((ldy & 1) || (reinterpret_cast<uintptr_t>(y) & 7)) return B200VQ_EALIGN;
+    const size_t smem = static_cast<size_t>(C) * (D + 4) * 4;
+    const unsigned blocks = static_cast<unsigned>((N + kLinRows - 1) / kLinRows);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = B200VQ_OK;
+#define B200VQ_LIN_OUT(DD)                                                           \
+    if ((rc = set_smem(linear_out_kernel<DD>, smem))) return rc;                     \
+    linear_out_kernel<DD><<<blocks, 256, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy)
+    switch (D) {
+        case 8: B200VQ_LIN_OUT(8); break;
+        case 16: B200VQ_LIN_OUT(16); break;
+        case 24: B200VQ_LIN_OUT(24); break;
+        default: B200VQ_LIN_OUT(32); break;
+    }
+#undef B200VQ_LIN_OUT
+    return launch_check();
+}
+
+int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
+                       float* colsum, b200vq_stream_t stream) {
+    if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
+    if (!dw) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = cuda_check(cudaMemsetAsync(dw, 0, static_cast<size_t>(C) * D * sizeof(float), st));
+    if (rc) return rc;
+    if (colsum && (rc = cuda_check(cudaMemsetAsync(colsum, 0, static_cast<size_t>(C) * sizeof(float), st)))) return rc;
+    if (N == 0) return B200VQ_OK;
+    if (!x || !y || ldx < C) return B200VQ_EINVAL;
+    if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15)) return B200VQ_EALIGN;
+    const int64_t tiles = (N + kWgTok - 1) / kWgTok;
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>(tiles, sm_count()));
+#define B200VQ_WG(DD)                                                                \
+    if ((rc = set_smem(weight_grad_kernel<DD>, wg_smem_bytes<DD>()))) return rc;     \
+    weight_grad_kernel<DD><<<blocks, 256, wg_smem_bytes<DD>(), st>>>(x, ldx, y, N, C, dw, dw_is_dc, colsum)
+    switch (D) {
+        case 8: B200VQ_WG(8); break;
+        case 16: B200VQ_WG(16); break;
+        case 24: B200VQ_WG(24); break;
+        default: B200VQ_WG(32); break;
+    }
+#undef B200VQ_WG
+    return launch_check();
+}
+
+int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream) {
+    if (N < 0 || D <= 0 || D > 32 || !out) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = cuda_check(cudaMemsetAsync(out, 0, static_cast<size_t>(D) * sizeof(float), st));
+    if (rc || N == 0) return rc;
+    if (!y) return B200VQ_EINVAL;
+    const int per = 256 / D;
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + per - 1) / per, 2ll * sm_count()));
+    colsum_small_kernel<<<blocks, 256, 0, st>>>(y, N, D, out);
     return launch_check();
 }
 

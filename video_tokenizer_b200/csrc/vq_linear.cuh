@@ -1,0 +1,288 @@
+// b200vq -- the Bottleneck's two skinny linears (in_linear C -> D, out_linear D -> C with
+// D <= 32 << C; reference models/bottleneck.py:109-110, :140-142, :162-164) and their backward.
+//
+// These GEMMs move 4*C bytes per token for 2*C*D flops: they are HBM-bound by a wide margin
+// (arithmetic intensity D/2 flop/byte), so they are written as streaming kernels that touch
+// each activation byte exactly once, with the tiny weight matrix resident in shared memory.
+// The contraction itself runs on warp-level tensor-core MMAs (mma.sync m16n8k8, TF32 inputs,
+// fp32 accumulate) so that instruction issue never limits the stream:
+//   * linear_in   (z = x W_in^T + b, decides the code indices) uses the 3xTF32 split
+//     x = xb + xs, w = wb + ws, x.w ~ xb.wb + xb.ws + xs.wb  (error ~ 2^-21, fp32-class);
+//   * linear_out / grad_x and the weight gradients use single-pass TF32 with round-to-nearest
+//     operands (norm-wise error ~ 3e-4, inside the 1e-3 parity tolerance).
+// Fragment layout of mma.sync.m16n8k8 (g = lane >> 2, t = lane & 3):
+//   A: a0 (row g, k t)  a1 (row g+8, k t)  a2 (row g, k t+4)  a3 (row g+8, k t+4)
+//   B: b0 (k t, col g)  b1 (k t+4, col g)
+//   C: c0 (row g, col 2t)  c1 (row g, col 2t+1)  c2 (row g+8, col 2t)  c3 (row g+8, col 2t+1)
+#pragma once
+#include "vq_common.cuh"
+
+namespace b200vq {
+
+__device__ __forceinline__ uint32_t tf32_rna(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ void tf32_split(float v, uint32_t& big, uint32_t& small) {
+    big = tf32_rna(v);
+    small = tf32_rna(v - __uint_as_float(big));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+                 "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
+
+// =======================================================================================
+// linear_in:  y[n][d] = sum_c x[n][c] * w[d][c] + b[d]      (x: N x C, row stride ldx; w: D x C)
+// One warp = 16 rows.  x streams straight from global memory into A fragments (one float4
+// per row per 16 columns: within a 16-column chunk lane t supplies columns 4t..4t+3, which
+// the MMA sees as k = t, t+4 of two consecutive k8 steps; w is read with the same mapping).
+// w lives in shared memory as fp32 (row stride C + 16 words: conflict-free LDS.128).
+// =======================================================================================
+template <int D>
+__global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
+                                                        const float* __restrict__ w, const float* __restrict__ bias,
+                                                        float* __restrict__ y) {
+    constexpr int NT = D / 8;
+    extern __shared__ float s_w[];  // [D][C + 16]
+    const int cs = C + 16;
+    for (int i = threadIdx.x; i < D * (C / 4); i += 256) {
+        const int d = i / (C / 4), c4 = i - d * (C / 4);
+        *reinterpret_cast<float4*>(&s_w[d * cs + 4 * c4]) = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(d) * C) + c4);
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinRows + warp * 16 + g;
+    const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
+    const float4* xa = reinterpret_cast<const float4*>(x + ra * ldx) + t;
+    const float4* xb = reinterpret_cast<const float4*>(x + rb * ldx) + t;
+    float acc[NT][4];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f; }
+    const int chunks = C / 16;
+    constexpr int PF = 4;  // chunks in flight per row
+    float4 va[PF], vb[PF];
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+        if (u < chunks) { va[u] = __ldg(xa + 4 * u); vb[u] = __ldg(xb + 4 * u); }
+    }
+    for (int c0 = 0; c0 < chunks; c0 += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int c = c0 + u;
+            if (c >= chunks) break;
+            const float4 a = va[u], b = vb[u];
+            if (c + PF < chunks) { va[u] = __ldg(xa + 4 * (c + PF)); vb[u] = __ldg(xb + 4 * (c + PF)); }
+            uint32_t ab[4], as[4], bb[4], bs[4];
+            tf32_split(a.x, ab[0], as[0]); tf32_split(a.y, ab[1], as[1]); tf32_split(a.z, ab[2], as[2]); tf32_split(a.w, ab[3], as[3]);
+            tf32_split(b.x, bb[0], bs[0]); tf32_split(b.y, bb[1], bs[1]); tf32_split(b.z, bb[2], bs[2]); tf32_split(b.w, bb[3], bs[3]);
+#pragma unroll
+            for (int j = 0; j < NT; ++j) {
+                const float4 wv = *reinterpret_cast<const float4*>(&s_w[(8 * j + g) * cs + 16 * c + 4 * t]);
+                uint32_t wb[4], ws[4];
+                tf32_split(wv.x, wb[0], ws[0]); tf32_split(wv.y, wb[1], ws[1]); tf32_split(wv.z, wb[2], ws[2]); tf32_split(wv.w, wb[3], ws[3]);
+                // step 0: columns 4t, 4t+1 ; step 1: columns 4t+2, 4t+3.  small terms first.
+                mma_tf32(acc[j], as[0], bs[0], as[1], bs[1], wb[0], wb[1]);
+                mma_tf32(acc[j], ab[0], bb[0], ab[1], bb[1], ws[0], ws[1]);
+                mma_tf32(acc[j], as[2], bs[2], as[3], bs[3], wb[2], wb[3]);
+                mma_tf32(acc[j], ab[2], bb[2], ab[3], bb[3], ws[2], ws[3]);
+                mma_tf32(acc[j], ab[0], bb[0], ab[1], bb[1], wb[0], wb[1]);
+                mma_tf32(acc[j], ab[2], bb[2], ab[3], bb[3], wb[2], wb[3]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+        const int d = 8 * j + 2 * t;
+        const float b0 = bias ? __ldg(bias + d) : 0.f, b1 = bias ? __ldg(bias + d + 1) : 0.f;
+        if (r0 < N) *reinterpret_cast<float2*>(y + r0 * D + d) = make_float2(acc[j][0] + b0, acc[j][1] + b1);
+        if (r0 + 8 < N) *reinterpret_cast<float2*>(y + (r0 + 8) * D + d) = make_float2(acc[j][2] + b0, acc[j][3] + b1);
+    }
+}
+
+// =======================================================================================
+// linear_out:  y[n][c] = sum_d a[n][d] * w'[c][d] + b[c]     (a: N x D; y: N x C, row stride ldy)
+// w' is given either as [C][D] (w_is_dc = 0: out_linear.weight) or as [D][C] (w_is_dc = 1:
+// in_linear.weight, for grad_x = grad_z W_in).  It is kept in shared memory as TF32,
+// [C][D + 4] (conflict-free B fragments).  One warp = 16 rows x all C columns.
+// =======================================================================================
+template <int D>
+__global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict__ a, int64_t N, const float* __restrict__ w,
+                                                         int w_is_dc, const float* __restrict__ bias, int C,
+                                                         float* __restrict__ y, int64_t ldy) {
+    constexpr int KS = D / 8, DS = D + 4;
+    extern __shared__ float s_w[];  // [C][D + 4] tf32 bits
+    for (int i = threadIdx.x; i < C * D; i += 256) {
+        int c, d;
+        if (w_is_dc) { d = i / C; c = i - d * C; } else { c = i / D; d = i - c * D; }
+        s_w[c * DS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinRows + warp * 16 + g;
+    const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
+    uint32_t fa[KS][4];
+#pragma unroll
+    for (int s = 0; s < KS; ++s) {
+        fa[s][0] = tf32_rna(__ldg(a + ra * D + 8 * s + t));
+        fa[s][1] = tf32_rna(__ldg(a + rb * D + 8 * s + t));
+        fa[s][2] = tf32_rna(__ldg(a + ra * D + 8 * s + t + 4));
+        fa[s][3] = tf32_rna(__ldg(a + rb * D + 8 * s + t + 4));
+    }
+    float* ya = y + r0 * ldy + 2 * t;
+    float* yb = y + (r0 + 8) * ldy + 2 * t;
+    const bool oka = r0 < N, okb = r0 + 8 < N;
+#pragma unroll 4
+    for (int j = 0; j < C / 8; ++j) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* wr = &s_w[(8 * j + g) * DS + t];
+#pragma unroll
+        for (int s = 0; s < KS; ++s)
+            mma_tf32(acc, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(wr[8 * s]), __float_as_uint(wr[8 * s + 4]));
+        const float b0 = bias ? __ldg(bias + 8 * j + 2 * t) : 0.f, b1 = bias ? __ldg(bias + 8 * j + 2 * t + 1) : 0.f;
+        if (oka) *reinterpret_cast<float2*>(ya + 8 * j) = make_float2(acc[0] + b0, acc[1] + b1);
+        if (okb) *reinterpret_cast<float2*>(yb + 8 * j) = make_float2(acc[2] + b0, acc[3] + b1);
+    }
+}
+
+// =======================================================================================
+// weight_grad:  dw[c][d] += sum_n x[n][c] * y[n][d]     colsum[c] += sum_n x[n][c]
+// (x: N x C row stride ldx -- the activation or the upstream gradient; y: N x D.)
+// Used for out_linear.weight.grad (x = grad_output, y = regularized_z; colsum = bias grad)
+// and in_linear.weight.grad (x = the layer input, y = grad_z; written transposed, [d][c]).
+// The output tile is [C][D] with tokens as the contraction: a CTA walks 128-column chunks
+// (outer) and its share of 128-token tiles (inner); warp w owns columns 16w..16w+15 of the
+// chunk, so its 16 x D accumulators stay in registers across all of the CTA's token tiles and
+// are flushed with one atomicAdd per element per chunk.  x tiles are staged through shared
+// memory with cp.async (double buffered): each x byte is read from HBM once.
+// =======================================================================================
+constexpr int kWgCols = 128;            // columns per chunk (8 warps x 16)
+constexpr int kWgTok = 128;             // tokens per tile
+constexpr int kWgStride = kWgCols + 8;  // 136 = 8 mod 32: conflict-free transposed A fragments
+
+template <int D>
+__host__ __device__ constexpr int wg_ystride() { return (D % 32 == 8 || D % 32 == 24) ? D : D + 8; }
+template <int D>
+__host__ __device__ constexpr size_t wg_smem_bytes() {
+    return (2 * static_cast<size_t>(kWgTok) * kWgStride + 2 * static_cast<size_t>(kWgTok) * wg_ystride<D>()) * 4;
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) weight_grad_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ y,
+                                                          int64_t N, int C, float* __restrict__ dw, int dw_is_dc,
+                                                          float* __restrict__ colsum) {
+    constexpr int NT = D / 8, YS = wg_ystride<D>();
+    extern __shared__ float s_wg[];
+    float* s_x = s_wg;                                  // [2][128 tok][136]
+    float* s_y = s_wg + 2 * kWgTok * kWgStride;         // [2][128 tok][YS]   (tf32 bits after conversion)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int64_t tiles = (N + kWgTok - 1) / kWgTok;
+    const int chunks = (C + kWgCols - 1) / kWgCols;
+
+    auto stage = [&](int buf, int64_t tile, int chunk) {
+        // x block: 128 tokens x 128 columns (zero beyond N / C), y tile: 128 tokens x D
+        const int64_t tok0 = tile * kWgTok;
+        const int col0 = chunk * kWgCols;
+        float* dx = s_x + buf * kWgTok * kWgStride;
+        for (int i = threadIdx.x; i < kWgTok * (kWgCols / 4); i += 256) {
+            const int r = i / (kWgCols / 4), c4 = i - r * (kWgCols / 4);
+            float* dst = dx + r * kWgStride + 4 * c4;
+            if (tok0 + r < N && col0 + 4 * c4 < C) cp_async16(dst, x + (tok0 + r) * ldx + col0 + 4 * c4);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        float* dy = s_y + buf * kWgTok * YS;
+        for (int i = threadIdx.x; i < kWgTok * (D / 4); i += 256) {
+            const int r = i / (D / 4), d4 = i - r * (D / 4);
+            float* dst = dy + r * YS + 4 * d4;
+            if (tok0 + r < N) cp_async16(dst, y + (tok0 + r) * D + 4 * d4);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        cp_async_commit();
+    };
+
+    for (int chunk = 0; chunk < chunks; ++chunk) {
+        float acc[NT][4];
+#pragma unroll
+        for (int j = 0; j < NT; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f; }
+        float cs0 = 0.f, cs1 = 0.f;  // column sums of columns g and g+8 over this lane's tokens
+        int buf = 0;
+        int64_t tile = blockIdx.x;
+        if (tile < tiles) stage(0, tile, chunk);
+        for (; tile < tiles; tile += gridDim.x) {
+            const int64_t next = tile + gridDim.x;
+            if (next < tiles) { stage(buf ^ 1, next, chunk); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+            __syncthreads();
+            const float* bx = s_x + buf * kWgTok * kWgStride + 16 * warp;
+            const float* by = s_y + buf * kWgTok * YS;
+#pragma unroll 4
+            for (int s = 0; s < kWgTok / 8; ++s) {
+                // A = x^T: (row = column g / g+8 of the chunk, k = token 8s+t / 8s+t+4)
+                const float x0 = bx[(8 * s + t) * kWgStride + g], x1 = bx[(8 * s + t) * kWgStride + g + 8];
+                const float x2 = bx[(8 * s + t + 4) * kWgStride + g], x3 = bx[(8 * s + t + 4) * kWgStride + g + 8];
+                cs0 += x0 + x2;
+                cs1 += x1 + x3;
+                const uint32_t a0 = tf32_rna(x0), a1 = tf32_rna(x1), a2 = tf32_rna(x2), a3 = tf32_rna(x3);
+#pragma unroll
+                for (int j = 0; j < NT; ++j) {
+                    const uint32_t b0 = tf32_rna(by[(8 * s + t) * YS + 8 * j + g]);
+                    const uint32_t b1 = tf32_rna(by[(8 * s + t + 4) * YS + 8 * j + g]);
+                    mma_tf32(acc[j], a0, a1, a2, a3, b0, b1);
+                }
+            }
+            __syncthreads();
+            buf ^= 1;
+        }
+        // flush this chunk: c0/c1 -> (column g, d 2t / 2t+1), c2/c3 -> (column g+8, ...)
+        const int ca = chunk * kWgCols + 16 * warp + g, cb = ca + 8;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) {
+            const int d = 8 * j + 2 * t;
+            if (ca < C) {
+                atomicAdd(dw + (dw_is_dc ? static_cast<int64_t>(d) * C + ca : static_cast<int64_t>(ca) * D + d), acc[j][0]);
+                atomicAdd(dw + (dw_is_dc ? static_cast<int64_t>(d + 1) * C + ca : static_cast<int64_t>(ca) * D + d + 1), acc[j][1]);
+            }
+            if (cb < C) {
+                atomicAdd(dw + (dw_is_dc ? static_cast<int64_t>(d) * C + cb : static_cast<int64_t>(cb) * D + d), acc[j][2]);
+                atomicAdd(dw + (dw_is_dc ? static_cast<int64_t>(d + 1) * C + cb : static_cast<int64_t>(cb) * D + d + 1), acc[j][3]);
+            }
+        }
+        if (colsum) {
+            cs0 += __shfl_xor_sync(0xffffffffu, cs0, 1); cs0 += __shfl_xor_sync(0xffffffffu, cs0, 2);
+            cs1 += __shfl_xor_sync(0xffffffffu, cs1, 1); cs1 += __shfl_xor_sync(0xffffffffu, cs1, 2);
+            if (t == 0) {
+                if (ca < C) atomicAdd(colsum + ca, cs0);
+                if (cb < C) atomicAdd(colsum + cb, cs1);
+            }
+        }
+    }
+}
+
+// column sums of a small N x D matrix (in_linear.bias.grad = sum_n grad_z[n][:])
+__global__ void __launch_bounds__(256) colsum_small_kernel(const float* __restrict__ y, int64_t N, int D, float* __restrict__ out) {
+    // thread (r, d): r = threadIdx.x / D strides over rows
+    __shared__ float s_acc[32];
+    if (threadIdx.x < 32) s_acc[threadIdx.x] = 0.f;
+    __syncthreads();
+    const int per = 256 / D, d = threadIdx.x % D, r = threadIdx.x / D;
+    float acc = 0.f;
+    if (r < per)
+        for (int64_t n = static_cast<int64_t>(blockIdx.x) * per + r; n < N; n += static_cast<int64_t>(gridDim.x) * per) acc += y[n * D + d];
+    if (r < per) atomicAdd(&s_acc[d], acc);
+    __syncthreads();
+    if (threadIdx.x < D) atomicAdd(out + threadIdx.x, s_acc[threadIdx.x]);
+}
+
+}  // namespace b200vq

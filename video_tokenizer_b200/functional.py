@@ -191,6 +191,137 @@ def vq_quantize(z, weight, *, mode, l2norm, t_inv=1.0, beta=0.25, w_cb=1.0, n_fi
                              int(n_first), int(seed), int(offset))
 
 
+# "fused": the Bottleneck's in/out linears run through the streaming kernels of libb200vq.so when
+# the shapes allow (fp32, D in {8,16,24,32}, C % 16 == 0, no autocast); "torch": always F.linear.
+LINEARS = os.environ.get("B200VQ_LINEARS", "fused")
+
+
+def set_linears(kind: str) -> str:
+    global LINEARS
+    if kind not in ("fused", "torch"):
+        raise ValueError("linears must be 'fused' or 'torch'")
+    prev, LINEARS = LINEARS, kind
+    return prev
+
+
+def linears_supported(x: torch.Tensor, weight: torch.Tensor, C: int, D: int) -> bool:
+    if LINEARS != "fused" or not x.is_cuda or x.dtype != torch.float32 or weight.dtype != torch.float32:
+        return False
+    if torch.is_autocast_enabled():
+        return False
+    return bool(_lib.load().b200vq_linear_supported(C, D))
+
+
+def _rows2d(x: torch.Tensor) -> Tuple[torch.Tensor, int, int]:
+    """(tensor, row stride, N) for a (..., C) tensor viewed as N rows; copies unless row-uniform
+    with a 16-byte aligned base and a stride that is a multiple of 4 elements."""
+    C = x.shape[-1]
+    t, stride = rows_view(x) if x.dim() in (2, 3) else (x.contiguous(), C)
+    if stride % 4 or t.data_ptr() % 16:
+        t, stride = x.contiguous(), C
+    return t, stride, t.shape[:-1].numel()
+
+
+class _LinearIn(torch.autograd.Function):
+    """z = x W^T + b with W (D, C): b200vq_linear_in; backward = b200vq_linear_out (grad_x),
+    b200vq_weight_grad (grad_W as (D, C)), b200vq_colsum (grad_b)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        lib = _lib.load()
+        D, C = weight.shape
+        xx, ldx, N = _rows2d(x.detach())
+        w = weight.detach().contiguous()
+        y = torch.empty(*x.shape[:-1], D, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.b200vq_linear_in(xx.data_ptr(), ldx, N, C, w.data_ptr(), _ptr(bias.detach() if bias is not None else None),
+                                            D, y.data_ptr(), _stream()), "b200vq_linear_in")
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        lib = _lib.load()
+        D, C = weight.shape
+        gy = gy.to(torch.float32).contiguous()
+        N = gy.numel() // D
+        gx = gw = gb = None
+        with torch.cuda.device(gy.device):
+            w = weight.detach().contiguous()
+            if ctx.needs_input_grad[0]:
+                gx = torch.empty(x.shape, dtype=torch.float32, device=gy.device)
+                _lib.check(lib.b200vq_linear_out(gy.data_ptr(), N, D, w.data_ptr(), 1, None, C, gx.data_ptr(), C, _stream()),
+                           "b200vq_linear_out(grad_x)")
+            if ctx.needs_input_grad[1]:
+                xx, ldx, _ = _rows2d(x.detach())
+                gw = torch.empty(D, C, dtype=torch.float32, device=gy.device)
+                _lib.check(lib.b200vq_weight_grad(xx.data_ptr(), ldx, gy.data_ptr(), N, C, D, gw.data_ptr(), 1, None, _stream()),
+                           "b200vq_weight_grad(in_linear)")
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                gb = torch.empty(D, dtype=torch.float32, device=gy.device)
+                _lib.check(lib.b200vq_colsum(gy.data_ptr(), N, D, gb.data_ptr(), _stream()), "b200vq_colsum")
+        return gx, gw, gb
+
+
+class _LinearOut(torch.autograd.Function):
+    """y = a W^T + b with W (C, D): b200vq_linear_out; backward = b200vq_linear_in on W^T (grad_a),
+    b200vq_weight_grad (grad_W as (C, D), grad_b = column sums of grad_y)."""
+
+    @staticmethod
+    def forward(ctx, a, weight, bias):
+        lib = _lib.load()
+        C, D = weight.shape
+        aa = a.detach().to(torch.float32).contiguous()
+        N = aa.numel() // D
+        y = torch.empty(*a.shape[:-1], C, dtype=torch.float32, device=a.device)
+        with torch.cuda.device(a.device):
+            _lib.check(lib.b200vq_linear_out(aa.data_ptr(), N, D, weight.detach().contiguous().data_ptr(), 0,
+                                             _ptr(bias.detach() if bias is not None else None), C, y.data_ptr(), C, _stream()),
+                       "b200vq_linear_out")
+        ctx.save_for_backward(aa, weight)
+        ctx.has_bias = bias is not None
+        ctx.a_shape = tuple(a.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        aa, weight = ctx.saved_tensors
+        lib = _lib.load()
+        C, D = weight.shape
+        g, ldg, N = _rows2d(gy.to(torch.float32))
+        ga = gw = gb = None
+        with torch.cuda.device(gy.device):
+            if ctx.needs_input_grad[0]:
+                wt = weight.detach().t().contiguous()   # (D, C)
+                ga = torch.empty(ctx.a_shape, dtype=torch.float32, device=gy.device)
+                _lib.check(lib.b200vq_linear_in(g.data_ptr(), ldg, N, C, wt.data_ptr(), None, D, ga.data_ptr(), _stream()),
+                           "b200vq_linear_in(grad_a)")
+            if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+                gw = torch.empty(C, D, dtype=torch.float32, device=gy.device)
+                gb = torch.empty(C, dtype=torch.float32, device=gy.device) if ctx.has_bias else None
+                _lib.check(lib.b200vq_weight_grad(g.data_ptr(), ldg, aa.data_ptr(), N, C, D, gw.data_ptr(), 0, _ptr(gb), _stream()),
+                           "b200vq_weight_grad(out_linear)")
+        return ga, gw, gb
+
+
+def linear_in(x, weight, bias):
+    """in_linear through the streaming kernels when supported, else F.linear."""
+    D, C = weight.shape
+    if linears_supported(x, weight, C, D):
+        return _LinearIn.apply(x, weight, bias)
+    return torch.nn.functional.linear(x, weight, bias)
+
+
+def linear_out(a, weight, bias):
+    """out_linear through the streaming kernels when supported, else F.linear."""
+    C, D = weight.shape
+    if linears_supported(a, weight, C, D):
+        return _LinearOut.apply(a, weight, bias)
+    return torch.nn.functional.linear(a, weight, bias)
+
+
 def codebook_lookup(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, shape=None) -> torch.Tensor:
     """get_codebook_entry (bottleneck.py:327-341) through b200vq_decode."""
     _require_cuda(indices, "indices")
