@@ -452,7 +452,7 @@ extern "C" {
 
 int b200vq_linear_supported(int C, int D) {
     if (!lin_dim_ok(D) || C < 16 || (C % 16) != 0) return 0;
-    const size_t in_smem = static_cast<size_t>(D) * (C + 16) * 4, out_smem = static_cast<size_t>(C) * (D + 4) * 4;
+    const size_t in_smem = static_cast<size_t>(D) * (C + 16) * 4, out_smem = static_cast<size_t>(C) * (D + 5) * 4;
     return in_smem <= 200 * 1024 && out_smem <= 200 * 1024 ? 1 : 0;
 }
 
@@ -465,7 +465,7 @@ int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
         (reinterpret_cast<uintptr_t>(y) & 7))
         return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
-    const unsigned blocks = static_cast<unsigned>((N + kLinRows - 1) / kLinRows);
+    const unsigned blocks = static_cast<unsigned>((N + kLinInRows - 1) / kLinInRows);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
 #define B200VQ_LIN_IN(DD)                                                            \
@@ -487,7 +487,7 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     if (N == 0) return B200VQ_OK;
     if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
     if ((ldy & 1) || (reinterpret_cast<uintptr_t>(y) & 7)) return B200VQ_EALIGN;
-    const size_t smem = static_cast<size_t>(C) * (D + 4) * 4;
+    const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
     const unsigned blocks = static_cast<unsigned>((N + kLinRows - 1) / kLinRows);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
@@ -516,7 +516,7 @@ int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
     if (!x || !y || ldx < C) return B200VQ_EINVAL;
     if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15)) return B200VQ_EALIGN;
     const int64_t tiles = (N + kWgTok - 1) / kWgTok;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>(tiles, sm_count()));
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>(tiles, 2ll * sm_count()));
 #define B200VQ_WG(DD)                                                                \
     if ((rc = set_smem(weight_grad_kernel<DD>, wg_smem_bytes<DD>()))) return rc;     \
     weight_grad_kernel<DD><<<blocks, 256, wg_smem_bytes<DD>(), st>>>(x, ldx, y, N, C, dw, dw_is_dc, colsum)

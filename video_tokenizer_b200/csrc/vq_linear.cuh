@@ -52,6 +52,8 @@ constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 // the MMA sees as k = t, t+4 of two consecutive k8 steps; w is read with the same mapping).
 // w lives in shared memory as fp32 (row stride C + 16 words: conflict-free LDS.128).
 // =======================================================================================
+constexpr int kLinInRows = 256;  // linear_in: 8 warps x 32 rows (two m16 tiles share every w fragment)
+
 template <int D>
 __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
                                                         const float* __restrict__ w, const float* __restrict__ bias,
@@ -65,52 +67,70 @@ __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict_
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinRows + warp * 16 + g;
-    const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
-    const float4* xa = reinterpret_cast<const float4*>(x + ra * ldx) + t;
-    const float4* xb = reinterpret_cast<const float4*>(x + rb * ldx) + t;
-    float acc[NT][4];
+    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinInRows + warp * 32 + g;   // rows r0 + 8q, q = 0..3
+    const float4* xr[4];
 #pragma unroll
-    for (int j = 0; j < NT; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f; }
+    for (int q = 0; q < 4; ++q) xr[q] = reinterpret_cast<const float4*>(x + min(r0 + 8 * q, N - 1) * ldx) + t;
+    float acc[2][NT][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) { acc[m][j][0] = acc[m][j][1] = acc[m][j][2] = acc[m][j][3] = 0.f; }
     const int chunks = C / 16;
-    constexpr int PF = 4;  // chunks in flight per row
-    float4 va[PF], vb[PF];
+    constexpr int PF = 2;  // chunks in flight per row
+    float4 v[PF][4];
 #pragma unroll
-    for (int u = 0; u < PF; ++u) {
-        if (u < chunks) { va[u] = __ldg(xa + 4 * u); vb[u] = __ldg(xb + 4 * u); }
-    }
+    for (int u = 0; u < PF; ++u)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) if (u < chunks) v[u][q] = __ldg(xr[q] + 4 * u);
     for (int c0 = 0; c0 < chunks; c0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
             const int c = c0 + u;
             if (c >= chunks) break;
-            const float4 a = va[u], b = vb[u];
-            if (c + PF < chunks) { va[u] = __ldg(xa + 4 * (c + PF)); vb[u] = __ldg(xb + 4 * (c + PF)); }
-            uint32_t ab[4], as[4], bb[4], bs[4];
-            tf32_split(a.x, ab[0], as[0]); tf32_split(a.y, ab[1], as[1]); tf32_split(a.z, ab[2], as[2]); tf32_split(a.w, ab[3], as[3]);
-            tf32_split(b.x, bb[0], bs[0]); tf32_split(b.y, bb[1], bs[1]); tf32_split(b.z, bb[2], bs[2]); tf32_split(b.w, bb[3], bs[3]);
+            uint32_t xb[4][4], xs[4][4];   // [row q][column 4t + e]
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 a = v[u][q];
+                if (c + PF < chunks) v[u][q] = __ldg(xr[q] + 4 * (c + PF));
+                tf32_split(a.x, xb[q][0], xs[q][0]); tf32_split(a.y, xb[q][1], xs[q][1]);
+                tf32_split(a.z, xb[q][2], xs[q][2]); tf32_split(a.w, xb[q][3], xs[q][3]);
+            }
 #pragma unroll
             for (int j = 0; j < NT; ++j) {
                 const float4 wv = *reinterpret_cast<const float4*>(&s_w[(8 * j + g) * cs + 16 * c + 4 * t]);
                 uint32_t wb[4], ws[4];
                 tf32_split(wv.x, wb[0], ws[0]); tf32_split(wv.y, wb[1], ws[1]); tf32_split(wv.z, wb[2], ws[2]); tf32_split(wv.w, wb[3], ws[3]);
-                // step 0: columns 4t, 4t+1 ; step 1: columns 4t+2, 4t+3.  small terms first.
-                mma_tf32(acc[j], as[0], bs[0], as[1], bs[1], wb[0], wb[1]);
-                mma_tf32(acc[j], ab[0], bb[0], ab[1], bb[1], ws[0], ws[1]);
-                mma_tf32(acc[j], as[2], bs[2], as[3], bs[3], wb[2], wb[3]);
-                mma_tf32(acc[j], ab[2], bb[2], ab[3], bb[3], ws[2], ws[3]);
-                mma_tf32(acc[j], ab[0], bb[0], ab[1], bb[1], wb[0], wb[1]);
-                mma_tf32(acc[j], ab[2], bb[2], ab[3], bb[3], wb[2], wb[3]);
+                // step 0: columns 4t, 4t+1 ; step 1: columns 4t+2, 4t+3.  The tensor core adds into
+                // its accumulator with truncation, so every chunk starts from zero accumulators
+                // (one for the big.big terms, one for the corrections) and the running sum is kept
+                // in fp32 round-to-nearest on the CUDA cores.
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    const int qa = 2 * m, qb = 2 * m + 1;
+                    float cm[4] = {0.f, 0.f, 0.f, 0.f}, cc[4] = {0.f, 0.f, 0.f, 0.f};
+                    mma_tf32(cc, xs[qa][0], xs[qb][0], xs[qa][1], xs[qb][1], wb[0], wb[1]);
+                    mma_tf32(cc, xb[qa][0], xb[qb][0], xb[qa][1], xb[qb][1], ws[0], ws[1]);
+                    mma_tf32(cc, xs[qa][2], xs[qb][2], xs[qa][3], xs[qb][3], wb[2], wb[3]);
+                    mma_tf32(cc, xb[qa][2], xb[qb][2], xb[qa][3], xb[qb][3], ws[2], ws[3]);
+                    mma_tf32(cm, xb[qa][0], xb[qb][0], xb[qa][1], xb[qb][1], wb[0], wb[1]);
+                    mma_tf32(cm, xb[qa][2], xb[qb][2], xb[qa][3], xb[qb][3], wb[2], wb[3]);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) acc[m][j][e] += cm[e] + cc[e];
+                }
             }
         }
     }
 #pragma unroll
-    for (int j = 0; j < NT; ++j) {
-        const int d = 8 * j + 2 * t;
-        const float b0 = bias ? __ldg(bias + d) : 0.f, b1 = bias ? __ldg(bias + d + 1) : 0.f;
-        if (r0 < N) *reinterpret_cast<float2*>(y + r0 * D + d) = make_float2(acc[j][0] + b0, acc[j][1] + b1);
-        if (r0 + 8 < N) *reinterpret_cast<float2*>(y + (r0 + 8) * D + d) = make_float2(acc[j][2] + b0, acc[j][3] + b1);
-    }
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) {
+            const int d = 8 * j + 2 * t;
+            const float b0 = bias ? __ldg(bias + d) : 0.f, b1 = bias ? __ldg(bias + d + 1) : 0.f;
+            const int64_t ra = r0 + 16 * m, rb = ra + 8;
+            if (ra < N) *reinterpret_cast<float2*>(y + ra * D + d) = make_float2(acc[m][j][0] + b0, acc[m][j][1] + b1);
+            if (rb < N) *reinterpret_cast<float2*>(y + rb * D + d) = make_float2(acc[m][j][2] + b0, acc[m][j][3] + b1);
+        }
 }
 
 // =======================================================================================
@@ -124,7 +144,9 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
                                                          int w_is_dc, const float* __restrict__ bias, int C,
                                                          float* __restrict__ y, int64_t ldy) {
     constexpr int KS = D / 8, DS = D + 4;
-    extern __shared__ float s_w[];  // [C][D + 4] tf32 bits
+    extern __shared__ float s_w[];  // [C][D + 4] tf32 bits, then bias [C]
+    float* s_b = s_w + C * DS;
+    for (int i = threadIdx.x; i < C; i += 256) s_b[i] = bias ? __ldg(bias + i) : 0.f;
     for (int i = threadIdx.x; i < C * D; i += 256) {
         int c, d;
         if (w_is_dc) { d = i / C; c = i - d * C; } else { c = i / D; d = i - c * D; }
@@ -152,7 +174,8 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
 #pragma unroll
         for (int s = 0; s < KS; ++s)
             mma_tf32(acc, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(wr[8 * s]), __float_as_uint(wr[8 * s + 4]));
-        const float b0 = bias ? __ldg(bias + 8 * j + 2 * t) : 0.f, b1 = bias ? __ldg(bias + 8 * j + 2 * t + 1) : 0.f;
+        const float2 bb = *reinterpret_cast<const float2*>(&s_b[8 * j + 2 * t]);
+        const float b0 = bb.x, b1 = bb.y;
         if (oka) *reinterpret_cast<float2*>(ya + 8 * j) = make_float2(acc[0] + b0, acc[1] + b1);
         if (okb) *reinterpret_cast<float2*>(yb + 8 * j) = make_float2(acc[2] + b0, acc[3] + b1);
     }
@@ -170,7 +193,7 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
 // memory with cp.async (double buffered): each x byte is read from HBM once.
 // =======================================================================================
 constexpr int kWgCols = 128;            // columns per chunk (8 warps x 16)
-constexpr int kWgTok = 128;             // tokens per tile
+constexpr int kWgTok = 64;              // tokens per tile
 constexpr int kWgStride = kWgCols + 8;  // 136 = 8 mod 32: conflict-free transposed A fragments
 
 template <int D>
