@@ -243,9 +243,10 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
         if (sp > 1 && per < 4) break;
         const int real = (total_tiles + per - 1) / per;
         const double ctas = static_cast<double>(row_tiles) * real;
-        const double waves = std::ceil(ctas / sms);
-        // ~1.5 tiles of prologue/teardown per CTA; a sampling CTA also re-learns the row maxima
-        const double cost = waves * (per + 1.5 + (mode == B200VQ_MODE_SAMPLE ? 2.0 : 0.0));
+        // measured (tools/tc_probe.py): a CTA costs ~6.5 tiles of prologue/teardown on top of its tiles,
+        // and CTAs of later waves start as soon as an SM frees up
+        const double waves = ctas <= sms ? 1.0 : ctas / sms;
+        const double cost = waves * (per + 6.5);
         if (cost < best_cost) { best_cost = cost; best_splits = sp; }
     }
     if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
@@ -277,11 +278,30 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
         static_cast<const char*>(image) + static_cast<size_t>(total_tiles) * tc_tile_bytes(D));
     unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
     unsigned int* list = reinterpret_cast<unsigned int*>(scratch + N);
-    collect_undecided_kernel<<<static_cast<unsigned>((N + 255) / 256), 256, 0, st>>>(
-        k64, scratch, N, flags, mode == B200VQ_MODE_ARGMIN_DIST ? 1 : 0, list);
+#define B200VQ_GROUPS(DD, MM)                                                                                  \
+    resolve_groups_kernel<DD, T, MM><<<static_cast<unsigned>((N + kResolveRows - 1) / kResolveRows), 256, 0, st>>>(                      \
+        static_cast<const T*>(z), z_row_stride, N, emb, e2, K, k_offset, l2norm, k64, scratch, flags, list)
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        if (mode == B200VQ_MODE_ARGMIN_DIST) {
+            switch (D) {
+                case 8: B200VQ_GROUPS(8, B200VQ_MODE_ARGMIN_DIST); break;
+                case 16: B200VQ_GROUPS(16, B200VQ_MODE_ARGMIN_DIST); break;
+                case 24: B200VQ_GROUPS(24, B200VQ_MODE_ARGMIN_DIST); break;
+                default: B200VQ_GROUPS(32, B200VQ_MODE_ARGMIN_DIST); break;
+            }
+        } else {
+            switch (D) {
+                case 8: B200VQ_GROUPS(8, B200VQ_MODE_ARGMAX_COS); break;
+                case 16: B200VQ_GROUPS(16, B200VQ_MODE_ARGMAX_COS); break;
+                case 24: B200VQ_GROUPS(24, B200VQ_MODE_ARGMAX_COS); break;
+                default: B200VQ_GROUPS(32, B200VQ_MODE_ARGMAX_COS); break;
+            }
+        }
+    });
+#undef B200VQ_GROUPS
     rc = launch_check();
     if (rc) return rc;
-    const unsigned rblocks = static_cast<unsigned>(std::min<int64_t>(N, 8ll * sms));
+    const unsigned rblocks = static_cast<unsigned>(kRescoreSegs * std::min<int64_t>(N, 2ll * sms));
 #define B200VQ_RESOLVE(DD, MM)                                                                                \
     rescore_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, emb, e2, K,    \
                                                         k_offset, l2norm, k64, list, n_resolved)

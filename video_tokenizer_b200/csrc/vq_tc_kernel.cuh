@@ -50,6 +50,34 @@ __device__ __forceinline__ float max8(const uint32_t* v) {
     const float c = fmaxf(__uint_as_float(v[6]), __uint_as_float(v[7]));
     return fmaxf(fmaxf(a, b), c);
 }
+// Deterministic modes, branch-free.  Per chunk of 32 accumulator columns the lane forms the maxima of
+// its four groups of 8 codes (3-input FMNMX trees), tags each with its position in the two low
+// mantissa bits (a perturbation of <= 3 ulp, far inside kTcMargin) and takes the largest and
+// second largest of the four.  The row keeps: the largest tagged group maximum seen, the first code
+// of the chunk it came from, and the largest group maximum among all OTHER groups.  The winning
+// code is found afterwards by exact fp32 scoring of the winning group's 8 codes
+// (resolve_groups_kernel); rows whose two best groups are within kTcMargin are re-scored in full.
+constexpr float kTcMasked = -1e30f;   // masked (invalid) columns: finite so that tagging cannot make a NaN
+__device__ __forceinline__ float tag2(float v, uint32_t t) { return __uint_as_float((__float_as_uint(v) & ~3u) | t); }
+struct DetTrack {
+    float best, second;
+    uint32_t chunk;
+    __device__ __forceinline__ void add(const uint32_t* v, uint32_t chunk_code) {
+        const float q0 = tag2(max8(v), 0u), q1 = tag2(max8(v + 8), 1u);
+        const float q2 = tag2(max8(v + 16), 2u), q3 = tag2(max8(v + 24), 3u);
+        const float a = fmaxf(q0, q1), b = fminf(q0, q1), c = fmaxf(q2, q3), d = fminf(q2, q3);
+        const float m1 = fmaxf(a, c);
+        const float m2 = fmaxf(fmaxf(fminf(a, c), b), d);
+        second = fmaxf(fmaxf(second, fminf(m1, best)), m2);
+        chunk = m1 > best ? chunk_code : chunk;
+        best = fmaxf(best, m1);
+    }
+    __device__ __forceinline__ uint32_t code() const { return chunk + 8u * (__float_as_uint(best) & 3u); }
+};
+__device__ __forceinline__ void mask_tail32(uint32_t* v, int valid) {   // columns >= valid are no codes
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j >= valid) v[j] = __float_as_uint(kTcMasked);
+}
 __device__ __forceinline__ float ord_value(uint32_t o) {
     return __uint_as_float((o & 0x80000000u) ? (o ^ 0x80000000u) : ~o);
 }
@@ -292,6 +320,57 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     } else {
         // ===== epilogue groups: group g = warps 4g..4g+3, columns [128*(g&1), +128) of buffer g>>1 ==========
         const int grp = warp >> 2, buf = grp >> 1, half = grp & 1;
+        if constexpr (!SAMPLE) {
+            // ---- deterministic modes: branch-free chunk tracking, two register buffers in flight ----------
+            const uint32_t row_local = 32 * (warp & 3) + lane;
+            const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
+            DetTrack tr{kTcMasked, kTcMasked, first_code};
+            uint32_t va[32], vb[32];
+            for (int i = buf; i < ntiles; i += kTcBufs) {
+                const int64_t code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes + half * 128;
+                const uint32_t chunk_code = static_cast<uint32_t>(p.k_offset + code0);
+                const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
+                mbar_wait(bar_tfull + 8 * buf, (i / kTcBufs) & 1);
+                tc_fence_after();
+                if (half == 0 && (warp & 3) == 0 && lane == 0) mbar_arrive(bar_empty + 8 * (i % kTcStages));
+                if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
+                const bool ldon = !(p.debug & 16), mathon = !(p.debug & 8);
+                if (ldon) tmem_ld32(t_lane, va);
+                tmem_ld_wait32(va);
+                if (ldon) tmem_ld32(t_lane + 32, vb);
+                if (valid < 32) mask_tail32(va, valid);
+                if (mathon) tr.add(va, chunk_code);
+                tmem_ld_wait32(vb);
+                if (ldon) tmem_ld32(t_lane + 64, va);
+                if (valid < 64) mask_tail32(vb, valid - 32);
+                if (mathon) tr.add(vb, chunk_code + 32);
+                tmem_ld_wait32(va);
+                if (ldon) tmem_ld32(t_lane + 96, vb);
+                if (valid < 96) mask_tail32(va, valid - 64);
+                if (mathon) tr.add(va, chunk_code + 64);
+                tmem_ld_wait32(vb);
+                tc_fence_before();
+                mbar_arrive(bar_tempty + 8 * buf);   // this group's half of the buffer is in registers
+                if (valid < 128) mask_tail32(vb, valid - 96);
+                if (mathon) tr.add(vb, chunk_code + 96);
+            }
+            if (tr.best > 0.5f * kTcMasked) {
+                const unsigned long long old = atomicMax(s_key + row_local, make_key(tr.best, tr.code()));
+                // the loser of every key comparison is a runner-up candidate
+                atomicMax(s_second + row_local, orderable(fmaxf(tr.second, fminf(key_value(old), tr.best))));
+            }
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (grp == 0) {
+                const int64_t row = row0 + row_local;
+                if (row < p.N && ntiles > 0) {
+                    const unsigned long long mine = s_key[row_local];
+                    const unsigned long long old = atomicMax(p.keys + row, mine);
+                    float runner = ord_value(s_second[row_local]);
+                    if (old != 0ull) runner = fmaxf(runner, fminf(key_value(old), key_value(mine)));
+                    atomicMax(reinterpret_cast<unsigned int*>(p.second) + row, orderable(runner));
+                }
+            }
+        } else {
         Epi c;
         c.queue = s_queue + warp * kQueueSlots * kQueueWords;
         c.s_key = s_key;
@@ -385,6 +464,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 }
             }
         }
+        }  // SAMPLE
     }
     // ---- teardown ------------------------------------------------------------------------------------
     tc_fence_before();
@@ -395,33 +475,86 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
 // =======================================================================================
 // Exact re-scoring of the rows the tensor-core pass could not decide (runner-up within
 // kTcMargin of the best approximate score, or every row when the codebook has a non-unit
-// row and the mode ranks by distance).  collect_undecided_kernel compacts their row ids,
+// row and the mode ranks by distance).  resolve_groups_kernel lists their row ids,
 // rescore_kernel re-scans the codebook for one listed row per CTA iteration with the same
 // fp32 arithmetic as scores_kernel, so the final indices are bit-identical to the exact path.
 // list[0] = count, list[4 ..] = row ids.
 // =======================================================================================
-__global__ void __launch_bounds__(256) collect_undecided_kernel(const unsigned long long* __restrict__ keys,
-                                                                const float* __restrict__ second, int64_t N,
-                                                                const unsigned int* __restrict__ flags, int dist_mode,
-                                                                unsigned int* __restrict__ list) {
-    const bool all_rows = dist_mode && flags != nullptr && (*flags & 1u);
-    const int64_t row = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;
-    bool take = false;
-    if (row < N) {
-        const float best = key_value(keys[row]);
-        const uint32_t so = reinterpret_cast<const unsigned int*>(second)[row];
-        const float sec = so == 0u ? -INFINITY : ord_value(so);
-        take = all_rows || !(best - sec >= kTcMargin);
+// After tc_scores_kernel in a deterministic mode (64 rows per CTA; a thread per row decides and
+// normalises, then a warp per row scores the chunk): keys[row] holds (best chunk
+// maximum, first code of that chunk), second[row] the best maximum among the other chunks.
+//   decided rows (gap >= kTcMargin): lane l scores code chunk+l in exact fp32 -- the same arithmetic as
+//     scores_kernel / rescore_kernel -- and the warp's max-key (highest value, lowest index) replaces
+//     keys[row];
+//   undecided rows (or every row when the codebook has a non-unit row and the mode ranks by
+//     distance): appended to list[] for rescore_kernel.
+constexpr int kResolveRows = 64;   // rows per CTA of resolve_groups_kernel
+template <int D, typename T, int MODE>
+__global__ void __launch_bounds__(256) resolve_groups_kernel(const T* __restrict__ z, int64_t z_row_stride, int64_t N,
+                                                             const float* __restrict__ emb, const float* __restrict__ e2,
+                                                             int64_t K, int64_t k_offset, int l2norm,
+                                                             unsigned long long* __restrict__ keys,
+                                                             const float* __restrict__ second,
+                                                             const unsigned int* __restrict__ flags,
+                                                             unsigned int* __restrict__ list) {
+    __shared__ __align__(16) float s_z[kResolveRows][D + 4];   // normalised row, then |z|^2
+    __shared__ uint32_t s_code[kResolveRows];                   // first code of the winning chunk, or ~0: skip
+    const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kResolveRows;
+    const bool all_rows = MODE == B200VQ_MODE_ARGMIN_DIST && flags != nullptr && (*flags & 1u);
+    if (threadIdx.x < kResolveRows) {   // one thread per row: decide, normalise once
+        const int64_t row = row0 + threadIdx.x;
+        uint32_t code = 0xFFFFFFFFu;
+        if (row < N) {
+            const unsigned long long key = keys[row];
+            const uint32_t so = reinterpret_cast<const unsigned int*>(second)[row];
+            const float sec = so == 0u ? -INFINITY : ord_value(so);
+            if (all_rows || !(key_value(key) - sec >= kTcMargin)) {
+                list[4 + atomicAdd(list, 1u)] = static_cast<unsigned int>(row);
+                keys[row] = 0ull;   // rescore_kernel merges its code segments with atomicMax
+            } else {
+                float zn[D];
+                float z2, zlen;
+                load_normalised_row<D, T>(z + row * z_row_stride, l2norm, zn, z2, zlen);
+#pragma unroll
+                for (int d = 0; d < D; ++d) s_z[threadIdx.x][d] = zn[d];
+                s_z[threadIdx.x][D] = z2;
+                code = key_code(key);
+            }
+        }
+        s_code[threadIdx.x] = code;
     }
-    const uint32_t b = __ballot_sync(0xffffffffu, take);
-    if (b) {
-        uint32_t base = 0;
-        if ((threadIdx.x & 31) == 0) base = atomicAdd(list, static_cast<unsigned int>(__popc(b)));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (take) list[4 + base + __popc(b & ((1u << (threadIdx.x & 31)) - 1u))] = static_cast<unsigned int>(row);
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int it = 0; it < kResolveRows / 32; ++it) {   // a warp takes 4 rows at a time, 8 lanes (codes) per row
+        const int r = it * 32 + warp * 4 + (lane >> 3);
+        const uint32_t code = s_code[r];
+        const int64_t k = static_cast<int64_t>(code) - k_offset + (lane & 7);
+        unsigned long long mine = 0ull;
+        if (code != 0xFFFFFFFFu && k < K) {
+            const float* e = emb + k * D;
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d < D; d += 4) {
+                const float4 ev = __ldg(reinterpret_cast<const float4*>(e + d));
+                const float4 zv = *reinterpret_cast<const float4*>(&s_z[r][d]);
+                acc = fmaf(zv.x, ev.x, acc);
+                acc = fmaf(zv.y, ev.y, acc);
+                acc = fmaf(zv.z, ev.z, acc);
+                acc = fmaf(zv.w, ev.w, acc);
+            }
+            mine = make_key(rank_value<MODE>(acc, s_z[r][D], __ldg(e2 + k), 1.0f, 0.f), static_cast<uint32_t>(k_offset + k));
+        }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, mine, o);
+            mine = other > mine ? other : mine;
+        }
+        if ((lane & 7) == 0 && code != 0xFFFFFFFFu) keys[row0 + r] = mine;
     }
 }
 
+constexpr int kRescoreSegs = 8;   // CTAs that share one listed row (each scans K / 8 codes)
 template <int D, typename T, int MODE>
 __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ z, int64_t z_row_stride,
                                                       const float* __restrict__ emb, const float* __restrict__ e2,
@@ -432,15 +565,18 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ z, i
     __shared__ unsigned long long s_red[8];
     const unsigned int count = list[0];
     if (blockIdx.x == 0 && threadIdx.x == 0 && n_resolved) atomicAdd(n_resolved, count);
-    for (unsigned int it = blockIdx.x; it < count; it += gridDim.x) {
+    const unsigned int seg = blockIdx.x % kRescoreSegs;
+    const int64_t per = (K + kRescoreSegs - 1) / kRescoreSegs;
+    const int64_t k_begin = seg * per, k_end = min(K, k_begin + per);
+    for (unsigned int it = blockIdx.x / kRescoreSegs; it < count; it += gridDim.x / kRescoreSegs) {
         const int64_t r = list[4 + it];
         float zn[D];
         float z2, zlen;
         load_normalised_row<D, T>(z + r * z_row_stride, l2norm, zn, z2, zlen);
         float best_v = -INFINITY;
-        uint32_t best_k = static_cast<uint32_t>(k_offset);
+        uint32_t best_k = static_cast<uint32_t>(k_offset + k_begin);
 #pragma unroll 4
-        for (int64_t k = threadIdx.x; k < K; k += 256) {
+        for (int64_t k = k_begin + threadIdx.x; k < k_end; k += 256) {
             const float* e = emb + k * D;
             float acc = 0.f;
 #pragma unroll
@@ -454,7 +590,7 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ z, i
             const float v = rank_value<MODE>(acc, z2, __ldg(e2 + k), 1.0f, 0.f);
             if (v > best_v) { best_v = v; best_k = static_cast<uint32_t>(k_offset + k); }
         }
-        unsigned long long key = make_key(best_v, best_k);
+        unsigned long long key = k_begin < k_end ? make_key(best_v, best_k) : 0ull;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
@@ -466,7 +602,7 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ z, i
             unsigned long long m = s_red[0];
 #pragma unroll
             for (int w = 1; w < 8; ++w) m = s_red[w] > m ? s_red[w] : m;
-            keys[r] = m;
+            atomicMax(keys + r, m);   // resolve_groups_kernel zeroed the keys of listed rows
         }
         __syncthreads();
     }
