@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 102
+#define B200VQ_VERSION 103
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -243,6 +243,36 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
 int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
                        int dw_is_dc, float* colsum, b200vq_stream_t stream);
 int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream);
+
+/*
+ * Whole-Bottleneck step in ONE host call per direction (Bottleneck.forward, bottleneck.py:170-188:
+ * in_linear -> quantizer -> out_linear, plus the trainer's usage statistics; and its autograd).
+ * Same kernels as the piecewise entry points above, enqueued back to back on `stream`; exists so
+ * that a training step costs two host calls instead of ~40.  fp32 x, b200vq_linear_supported(C, D).
+ *   forward  outputs: z (N,D) 'projected_z'; emb (K,D) + wnorm (K) (saved for backward); znorm, ste (N,D);
+ *            idx (N) int64; zlen (N); hist, hist_first (K) int32; losses (3); usage4 (4, nullable:
+ *            index_usage, index_usage_batch, kl_uni, perplexity); out (N,C; row stride ldo) 'output'
+ *   backward inputs: g_out (N,C; ldg) grad of 'output' (nullable); g_losses (3, device, nullable);
+ *            g_ste / g_znorm / g_z (N,D) and g_emb (K,D): extra grads on 'regularized_z',
+ *            'unregularized_z', 'projected_z', 'emb' (all nullable); the tensors saved by forward
+ *   backward outputs (each nullable = not needed): grad_x (N,C; ldgx), grad_w_in (D,C), grad_b_in (D),
+ *            grad_weight (K,D), grad_w_out (C,D), grad_b_out (C)
+ *   workspace >= b200vq_bottleneck_workspace_bytes(N,C,D,K), 16-byte aligned, same buffer both ways
+ */
+size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K);
+int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
+                              const float* weight, int64_t K, int D, const float* w_out, const float* b_out, int mode,
+                              int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
+                              float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
+                              int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
+                              float* out, int64_t ldo, void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
+int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
+                               const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
+                               int64_t N, int C, const float* w_in, const float* w_out, const float* emb,
+                               const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,
+                               const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
+                               int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
+                               float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
 
 #ifdef __cplusplus
 }

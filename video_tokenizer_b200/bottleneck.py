@@ -111,10 +111,8 @@ class SimpleVectorQuantizer(AbstractRegularizer):
             return _lib.MODE_ARGMAX_COS if (self.eval_deterministic and not self.training) else _lib.MODE_SAMPLE
         return _lib.MODE_ARGMIN_DIST
 
-    @torch.autocast(device_type="cuda", enabled=False)
-    def forward(self, z):
-        assert len(z.shape) == 3, "Input shape must be (batch, n_tokens, e_dim)"
-        VF._require_cuda(z, "z")
+    def _step_config(self, device):
+        """(mode, 1/T, philox seed, philox offset) of this call, after the reference's checks."""
         if self.stochastic:
             assert self.l2_normalized, "Stochastic sampling requires l2 normalization"
             if self.entropy_loss_weight > 0:
@@ -123,11 +121,41 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         t_inv = float(self.stochastic_temperature_inv) if self.stochastic else 1.0
         seed = offset = 0
         if mode == _lib.MODE_SAMPLE:
-            seed, offset = VF.philox_state(z.device)
+            seed, offset = VF.philox_state(device)
+        return mode, t_inv, seed, offset
+
+    def _assemble(self, z_shape, znorm, emb, ste, idx, losses, hist, hist_first, usage=None):
+        """Output dict of forward() (bottleneck.py:312-323) for entropy_loss_weight == 0."""
+        self.last_usage = (hist_first, hist)
+        self._last_stats = usage
+        zero = torch.zeros((), device=znorm.device, dtype=torch.float32)
+        out = {
+            "unregularized_z": znorm,
+            "emb": emb,
+            "regularized_z": ste,
+            "bottleneck_rep": idx.reshape(z_shape[0], z_shape[1]) if self.same_index_shape else idx,
+            "loss_q": losses[0],
+            "loss_commit": losses[1],
+            "loss_codebook": losses[2],
+            "loss_entropy": zero,
+            "per_sample_entropy": zero,
+            "codebook_entropy": zero,
+        }
+        if self.return_usage:
+            st = usage if usage is not None else VF.usage_stats(hist_first, hist)
+            out.update(index_usage=st[0], index_usage_batch=st[1], kl_uni=st[2], perplexity=st[3])
+        return out
+
+    @torch.autocast(device_type="cuda", enabled=False)
+    def forward(self, z):
+        assert len(z.shape) == 3, "Input shape must be (batch, n_tokens, e_dim)"
+        VF._require_cuda(z, "z")
+        mode, t_inv, seed, offset = self._step_config(z.device)
         znorm, emb, ste, idx, losses, hist, hist_first = VF.vq_quantize(
             z, self.embedding.weight, mode=mode, l2norm=self.l2_normalized, t_inv=t_inv, beta=self.beta,
             w_cb=self.codebook_loss_weight, n_first=z.shape[1], seed=seed, offset=offset)
         self.last_usage = (hist_first, hist)
+        self._last_stats = None
         loss_commit, loss_codebook = losses[1], losses[2]
         if self.entropy_loss_weight > 0:
             # N x K by definition (reference :300-303); torch on the device, weight is 0 in all cfgs
@@ -163,6 +191,8 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         forward (trainers/larp_tokenizer_trainer.py:335-352), computed from the fused histograms."""
         if self.last_usage is None:
             raise RuntimeError("code_usage() needs a forward pass first")
+        if getattr(self, "_last_stats", None) is not None:   # the one-call Bottleneck step already made them
+            return self._last_stats
         return VF.usage_stats(*self.last_usage)
 
     def get_codebook_entry(self, indices, shape=None):
@@ -257,6 +287,26 @@ class Bottleneck(nn.Module):
             input_norm_last = torch.linalg.vector_norm(x[:, -1, :].float(), dim=-1).mean()
         if self.sync_diagnostics:
             input_norm_first, input_norm_last = input_norm_first.item(), input_norm_last.item()
+        reg = self.regularizer
+        if (self.norm is None and type(reg) is SimpleVectorQuantizer and reg.entropy_loss_weight == 0
+                and self.project_dim == self.bottleneck_dim and len(x.shape) == 3 and self.in_linear.bias is not None
+                and VF.bottleneck_supported(x, self.in_linear.weight, reg.embedding.weight, self.out_linear.weight)):
+            # one host call per direction: in_linear -> quantizer -> out_linear (+ usage statistics)
+            mode, t_inv, seed, offset = reg._step_config(x.device)
+            x_hat, projected_z, znorm, emb, ste, idx, losses, hists, usage = VF.bottleneck_step(
+                x, self.in_linear.weight, self.in_linear.bias, reg.embedding.weight, self.out_linear.weight,
+                self.out_linear.bias, mode=mode, l2norm=reg.l2_normalized, t_inv=t_inv, beta=reg.beta,
+                w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset)
+            regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, losses, hists[0], hists[1], usage)
+            bottleneck_rep = regularized_output.pop("bottleneck_rep")
+            return {
+                "output": x_hat,
+                "bottleneck_rep": bottleneck_rep,
+                "projected_z": projected_z,
+                "input_norm_first": input_norm_first,
+                "input_norm_last": input_norm_last,
+                **regularized_output,
+            }
         z = self.project_in(x)
         projected_z = z
         if self.regularizer is not None:

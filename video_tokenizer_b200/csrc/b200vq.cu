@@ -476,8 +476,9 @@ int b200vq_linear_supported(int C, int D) {
     return in_smem <= 200 * 1024 && out_smem <= 200 * 1024 ? 1 : 0;
 }
 
-int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D, float* y,
-                     b200vq_stream_t stream) {
+namespace {
+int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, int w_is_cd, const float* bias, int D,
+                     float* y, cudaStream_t st) {
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!x || !w || !y || ldx < C) return B200VQ_EINVAL;
@@ -486,11 +487,10 @@ int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
         return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
     const unsigned blocks = static_cast<unsigned>((N + kLinInRows - 1) / kLinInRows);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
 #define B200VQ_LIN_IN(DD)                                                            \
     if ((rc = set_smem(linear_in_kernel<DD>, smem))) return rc;                      \
-    linear_in_kernel<DD><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, bias, y)
+    linear_in_kernel<DD><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y)
     switch (D) {
         case 8: B200VQ_LIN_IN(8); break;
         case 16: B200VQ_LIN_IN(16); break;
@@ -499,6 +499,12 @@ int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
     }
 #undef B200VQ_LIN_IN
     return launch_check();
+}
+}  // namespace
+
+int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D, float* y,
+                     b200vq_stream_t stream) {
+    return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, static_cast<cudaStream_t>(stream));
 }
 
 int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
@@ -560,6 +566,117 @@ int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t 
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + per - 1) / per, 2ll * sm_count()));
     colsum_small_kernel<<<blocks, 256, 0, st>>>(y, N, D, out);
     return launch_check();
+}
+
+}  // extern "C"
+
+// ---- whole-Bottleneck entry points: one host call per direction ------------------------------------
+// (reference Bottleneck.forward, models/bottleneck.py:170-188, and its autograd)
+namespace {
+__global__ void add_inplace_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t n) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += src[i];
+}
+inline int add_inplace(float* dst, const float* src, int64_t n, cudaStream_t st) {
+    if (n <= 0) return B200VQ_OK;
+    add_inplace_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(dst, src, n);
+    return launch_check();
+}
+struct BnLayout {
+    size_t e2, image, vq, ga, gz, gemb, total;
+};
+inline BnLayout bn_layout(int64_t N, int D, int64_t K) {
+    BnLayout l;
+    size_t off = 0;
+    l.e2 = off; off += align_up(static_cast<size_t>(K) * 4);
+    l.image = off; off += align_up(b200vq_tc_image_bytes(K, D));
+    l.vq = off; off += align_up(b200vq_workspace_bytes(N, D, K));
+    l.ga = off; off += align_up(static_cast<size_t>(N) * D * 4);
+    l.gz = off; off += align_up(static_cast<size_t>(N) * D * 4);
+    l.gemb = off; off += align_up(static_cast<size_t>(K) * D * 4);
+    l.total = off;
+    return l;
+}
+}  // namespace
+
+extern "C" {
+
+size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K) {
+    (void)C;
+    if (N < 0 || K <= 0 || D <= 0) return 0;
+    return bn_layout(N, D, K).total;
+}
+
+int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
+                              const float* weight, int64_t K, int D, const float* w_out, const float* b_out, int mode,
+                              int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
+                              float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
+                              int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
+                              float* out, int64_t ldo, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+    if (N <= 0 || K <= 0 || !valid_mode(mode)) return B200VQ_EINVAL;
+    if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
+    if (!x || !w_in || !weight || !w_out || !z || !emb || !wnorm || !znorm || !ste || !idx || !zlen || !hist || !hist_first ||
+        !losses || !out)
+        return B200VQ_EINVAL;
+    const BnLayout l = bn_layout(N, D, K);
+    if (!workspace || workspace_bytes < l.total) return B200VQ_EWORKSPACE;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
+    char* ws = static_cast<char*>(workspace);
+    float* e2 = reinterpret_cast<float*>(ws + l.e2);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, st);
+    if (rc) return rc;
+    if ((rc = b200vq_prepare_codebook(weight, K, D, l2norm, emb, e2, wnorm, stream))) return rc;
+    void* image = nullptr;
+    if (use_tc && b200vq_tc_supported(D, l2norm, mode)) {
+        image = ws + l.image;
+        if ((rc = b200vq_prepare_codebook_tc(emb, K, D, image, stream))) return rc;
+    }
+    rc = b200vq_forward(z, B200VQ_DT_F32, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset, n_first, beta, w_cb,
+                        znorm, ste, idx, zlen, hist, hist_first, losses, ws + l.vq, b200vq_workspace_bytes(N, D, K), stream);
+    if (rc) return rc;
+    if (usage4 && (rc = b200vq_usage_stats(hist_first, hist, K, usage4, stream))) return rc;
+    return b200vq_linear_out(ste, N, D, w_out, 0, b_out, C, out, ldo, stream);
+}
+
+int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
+                               const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
+                               int64_t N, int C, const float* w_in, const float* w_out, const float* emb,
+                               const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,
+                               const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
+                               int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
+                               float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+    if (N <= 0 || K <= 0) return B200VQ_EINVAL;
+    if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
+    if (!x || !w_in || !w_out || !emb || !wnorm || !znorm || !zlen || !idx || !ste) return B200VQ_EINVAL;
+    const BnLayout l = bn_layout(N, D, K);
+    if (!workspace || workspace_bytes < l.total) return B200VQ_EWORKSPACE;
+    char* ws = static_cast<char*>(workspace);
+    float* ga = reinterpret_cast<float*>(ws + l.ga);      // grad of 'regularized_z'
+    float* gz = reinterpret_cast<float*>(ws + l.gz);      // grad of 'projected_z'
+    float* gemb = reinterpret_cast<float*>(ws + l.gemb);  // grad of the normalised codebook
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc;
+    const float* ga_in = g_ste;
+    if (g_out) {
+        // grad_a = g_out W_out ; grad_W_out = g_out^T ste ; grad_b_out = column sums of g_out
+        if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, st))) return rc;
+        if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
+        ga_in = ga;
+        if (grad_w_out && (rc = b200vq_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, stream))) return rc;
+    } else {
+        if (grad_w_out && (rc = cuda_check(cudaMemsetAsync(grad_w_out, 0, static_cast<size_t>(C) * D * 4, st)))) return rc;
+        if (grad_b_out && (rc = cuda_check(cudaMemsetAsync(grad_b_out, 0, static_cast<size_t>(C) * 4, st)))) return rc;
+    }
+    if ((rc = b200vq_backward(ga_in, g_znorm, g_losses, znorm, zlen, idx, emb, nullptr, 0, N, D, K, l2norm, N, beta, w_cb, gz,
+                              B200VQ_DT_F32, gemb, stream)))
+        return rc;
+    if (grad_weight && (rc = b200vq_codebook_backward(gemb, g_emb, emb, wnorm, K, D, l2norm, grad_weight, stream))) return rc;
+    if (g_z && (rc = add_inplace(gz, g_z, N * D, st))) return rc;
+    if (grad_x && (rc = b200vq_linear_out(gz, N, D, w_in, 1, nullptr, C, grad_x, ldgx, stream))) return rc;
+    if (grad_w_in && (rc = b200vq_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, stream))) return rc;
+    if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, stream))) return rc;
+    return B200VQ_OK;
 }
 
 }  // extern "C"

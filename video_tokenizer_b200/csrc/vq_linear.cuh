@@ -46,7 +46,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 
 // =======================================================================================
-// linear_in:  y[n][d] = sum_c x[n][c] * w[d][c] + b[d]      (x: N x C, row stride ldx; w: D x C)
+// linear_in:  y[n][d] = sum_c x[n][c] * w[d][c] + b[d]      (x: N x C, row stride ldx; w: D x C, or C x D when w_is_cd)
 // One warp = 16 rows.  x streams straight from global memory into A fragments (one float4
 // per row per 16 columns: within a 16-column chunk lane t supplies columns 4t..4t+3, which
 // the MMA sees as k = t, t+4 of two consecutive k8 steps; w is read with the same mapping).
@@ -56,14 +56,21 @@ constexpr int kLinInRows = 256;  // linear_in: 8 warps x 32 rows (two m16 tiles 
 
 template <int D>
 __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
-                                                        const float* __restrict__ w, const float* __restrict__ bias,
-                                                        float* __restrict__ y) {
+                                                        const float* __restrict__ w, int w_is_cd,
+                                                        const float* __restrict__ bias, float* __restrict__ y) {
     constexpr int NT = D / 8;
     extern __shared__ float s_w[];  // [D][C + 16]
     const int cs = C + 16;
-    for (int i = threadIdx.x; i < D * (C / 4); i += 256) {
-        const int d = i / (C / 4), c4 = i - d * (C / 4);
-        *reinterpret_cast<float4*>(&s_w[d * cs + 4 * c4]) = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(d) * C) + c4);
+    if (w_is_cd) {   // w given as [C][D] (out_linear.weight, for grad_a = grad_y W_out): transpose while staging
+        for (int i = threadIdx.x; i < C * D; i += 256) {
+            const int c = i / D, d = i - c * D;
+            s_w[d * cs + c] = __ldg(w + i);
+        }
+    } else {
+        for (int i = threadIdx.x; i < D * (C / 4); i += 256) {
+            const int d = i / (C / 4), c4 = i - d * (C / 4);
+            *reinterpret_cast<float4*>(&s_w[d * cs + 4 * c4]) = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(d) * C) + c4);
+        }
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;

@@ -347,3 +347,94 @@ def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Ten
         _lib.check(lib.b200vq_usage_stats(hist_first.data_ptr(), hist_batch.data_ptr(), hist_first.numel(),
                                           out.data_ptr(), _stream()), "b200vq_usage_stats")
     return out
+
+
+class _BottleneckFunction(torch.autograd.Function):
+    """Whole Bottleneck step (in_linear -> quantizer -> out_linear + usage statistics) in ONE host
+    call per direction: b200vq_bottleneck_forward / b200vq_bottleneck_backward.
+    Outputs: output, projected_z, znorm, emb, ste, idx, losses(3), hist, hist_first, usage(4)."""
+
+    @staticmethod
+    def forward(ctx, x, w_in, b_in, weight, w_out, b_out, cfg):
+        mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset = cfg
+        lib = _lib.load()
+        dev = x.device
+        D, C = w_in.shape
+        K = weight.shape[0]
+        xx, ldx, N = _rows2d(x.detach())
+        lead = x.shape[:-1]
+        f32 = dict(dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            out = torch.empty(*lead, C, **f32)
+            # one allocation for the (N, D) tensors: projected_z | znorm | ste
+            nd = torch.empty(3, *lead, D, **f32)
+            z, znorm, ste = nd[0], nd[1], nd[2]
+            emb = torch.empty(K, D, **f32)
+            small = torch.empty(K + N + 8, **f32)           # wnorm | zlen | losses(3) usage(4)
+            wnorm, zlen, losses, usage = small[:K], small[K:K + N], small[K + N:K + N + 3], small[K + N + 3:K + N + 7]
+            idx = torch.empty(N, dtype=torch.int64, device=dev)
+            hists = torch.empty(2, K, dtype=torch.int32, device=dev)
+            ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
+            use_tc = 1 if SCORING == "tc" else 0
+            rc = lib.b200vq_bottleneck_forward(
+                xx.data_ptr(), ldx, N, C, w_in.data_ptr(), _ptr(b_in), weight.data_ptr(), K, D, w_out.data_ptr(), _ptr(b_out),
+                mode, int(l2norm), t_inv, seed, offset, n_first, beta, w_cb, use_tc, z.data_ptr(), emb.data_ptr(),
+                wnorm.data_ptr(), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(), hists[0].data_ptr(),
+                hists[1].data_ptr(), losses.data_ptr(), usage.data_ptr(), out.data_ptr(), C, ws.data_ptr(), ws.numel(),
+                _stream())
+            _lib.check(rc, "b200vq_bottleneck_forward")
+        ctx.save_for_backward(x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste)
+        ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
+        ctx.mark_non_differentiable(idx, hists, usage)
+        return out, z, znorm, emb, ste, idx, losses, hists, usage
+
+    @staticmethod
+    def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_losses, _gh, _gu):
+        x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste = ctx.saved_tensors
+        l2norm, beta, w_cb, N, C, D, K, has_b_in, has_b_out = ctx.cfg
+        lib = _lib.load()
+        dev = x.device
+
+        def _f32c(t):
+            return None if t is None else t.to(torch.float32).contiguous()
+
+        g_z, g_znorm, g_emb, g_ste, g_losses = _f32c(g_z), _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste), _f32c(g_losses)
+        go, ldg = None, C
+        if g_out is not None:
+            go, ldg, _ = _rows2d(g_out.to(torch.float32))
+        need = ctx.needs_input_grad
+        f32 = dict(dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            xx, ldx, _ = _rows2d(x.detach())
+            gx = torch.empty(x.shape, **f32) if need[0] else None
+            gw_in = torch.empty(D, C, **f32) if need[1] else None
+            gb_in = torch.empty(D, **f32) if (has_b_in and need[2]) else None
+            gw = torch.empty(K, D, **f32) if need[3] else None
+            gw_out = torch.empty(C, D, **f32) if (need[4] or (has_b_out and need[5])) else None
+            gb_out = torch.empty(C, **f32) if (has_b_out and need[5]) else None
+            ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
+            rc = lib.b200vq_bottleneck_backward(
+                _ptr(go), ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,
+                w_in.data_ptr(), w_out.data_ptr(), emb.data_ptr(), wnorm.data_ptr(), znorm.data_ptr(), zlen.data_ptr(),
+                idx.data_ptr(), ste.data_ptr(), K, D, int(l2norm), beta, w_cb, _ptr(gx), C, _ptr(gw_in), _ptr(gb_in), _ptr(gw),
+                _ptr(gw_out), _ptr(gb_out), ws.data_ptr(), ws.numel(), _stream())
+            _lib.check(rc, "b200vq_bottleneck_backward")
+        return gx, gw_in, gb_in, gw, gw_out, gb_out, None
+
+
+def bottleneck_supported(x, w_in, weight, w_out) -> bool:
+    """The one-call path needs fp32 everything, contiguous parameters, no autocast and shapes the
+    streaming linear kernels take."""
+    D, C = w_in.shape
+    return (LINEARS == "fused" and x.is_cuda and x.dim() == 3 and x.dtype == torch.float32
+            and w_in.dtype == weight.dtype == w_out.dtype == torch.float32
+            and w_in.is_contiguous() and weight.is_contiguous() and w_out.is_contiguous()
+            and tuple(w_out.shape) == (w_out.shape[0], D) and weight.shape[1] == D
+            and not torch.is_autocast_enabled() and bool(_lib.load().b200vq_linear_supported(C, D))
+            and bool(_lib.load().b200vq_linear_supported(w_out.shape[0], D)) and w_out.shape[0] == C)
+
+
+def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset):
+    """-> (output, projected_z, znorm, emb, ste, idx(N,), losses(3), hists(2,K) [batch, first], usage(4))"""
+    cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset))
+    return _BottleneckFunction.apply(x, w_in, b_in, weight, w_out, b_out, cfg)
