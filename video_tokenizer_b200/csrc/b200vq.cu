@@ -478,7 +478,7 @@ int b200vq_linear_supported(int C, int D) {
 
 namespace {
 int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, int w_is_cd, const float* bias, int D,
-                     float* y, cudaStream_t st) {
+                     float* y, bool precise, cudaStream_t st) {
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!x || !w || !y || ldx < C) return B200VQ_EINVAL;
@@ -486,11 +486,16 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
         (reinterpret_cast<uintptr_t>(y) & 7))
         return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
-    const unsigned blocks = static_cast<unsigned>((N + kLinInRows - 1) / kLinInRows);
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinInRows - 1) / kLinInRows, 2ll * sm_count()));
     int rc = B200VQ_OK;
-#define B200VQ_LIN_IN(DD)                                                            \
-    if ((rc = set_smem(linear_in_kernel<DD>, smem))) return rc;                      \
-    linear_in_kernel<DD><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y)
+#define B200VQ_LIN_IN(DD)                                                                        \
+    if (precise) {                                                                               \
+        if ((rc = set_smem(linear_in_kernel<DD, true>, smem))) return rc;                        \
+        linear_in_kernel<DD, true><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y);  \
+    } else {                                                                                     \
+        if ((rc = set_smem(linear_in_kernel<DD, false>, smem))) return rc;                       \
+        linear_in_kernel<DD, false><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y); \
+    }
     switch (D) {
         case 8: B200VQ_LIN_IN(8); break;
         case 16: B200VQ_LIN_IN(16); break;
@@ -504,7 +509,7 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
 
 int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D, float* y,
                      b200vq_stream_t stream) {
-    return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, static_cast<cudaStream_t>(stream));
+    return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, true, static_cast<cudaStream_t>(stream));
 }
 
 int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
@@ -512,9 +517,9 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
-    if ((ldy & 1) || (reinterpret_cast<uintptr_t>(y) & 7)) return B200VQ_EALIGN;
+    if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & 15) || (reinterpret_cast<uintptr_t>(w) & 15)) return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
-    const unsigned blocks = static_cast<unsigned>((N + kLinRows - 1) / kLinRows);
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinRows - 1) / kLinRows, 2ll * sm_count()));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
 #define B200VQ_LIN_OUT(DD)                                                           \
@@ -624,7 +629,7 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
     char* ws = static_cast<char*>(workspace);
     float* e2 = reinterpret_cast<float*>(ws + l.e2);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, st);
+    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, true, st);
     if (rc) return rc;
     if ((rc = b200vq_prepare_codebook(weight, K, D, l2norm, emb, e2, wnorm, stream))) return rc;
     void* image = nullptr;
@@ -660,7 +665,7 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
     const float* ga_in = g_ste;
     if (g_out) {
         // grad_a = g_out W_out ; grad_W_out = g_out^T ste ; grad_b_out = column sums of g_out
-        if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, st))) return rc;
+        if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, false, st))) return rc;
         if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
         ga_in = ga;
         if (grad_w_out && (rc = b200vq_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, stream))) return rc;

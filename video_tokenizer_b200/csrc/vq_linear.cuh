@@ -54,8 +54,8 @@ constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 // =======================================================================================
 constexpr int kLinInRows = 256;  // linear_in: 8 warps x 32 rows (two m16 tiles share every w fragment)
 
-template <int D>
-__global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
+template <int D, bool PRECISE>
+__global__ void __launch_bounds__(256, 2) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
                                                         const float* __restrict__ w, int w_is_cd,
                                                         const float* __restrict__ bias, float* __restrict__ y) {
     constexpr int NT = D / 8;
@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict_
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinInRows + warp * 32 + g;   // rows r0 + 8q, q = 0..3
+    for (int64_t tile = blockIdx.x; tile * kLinInRows < N; tile += gridDim.x) {   // persistent: w is staged once per CTA
+    const int64_t r0 = tile * kLinInRows + warp * 32 + g;   // rows r0 + 8q, q = 0..3
     const float4* xr[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) xr[q] = reinterpret_cast<const float4*>(x + min(r0 + 8 * q, N - 1) * ldx) + t;
@@ -100,12 +101,17 @@ __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict_
             for (int q = 0; q < 4; ++q) {
                 const float4 a = v[u][q];
                 if (c + PF < chunks) v[u][q] = __ldg(xr[q] + 4 * (c + PF));
-                tf32_split(a.x, xb[q][0], xs[q][0]); tf32_split(a.y, xb[q][1], xs[q][1]);
-                tf32_split(a.z, xb[q][2], xs[q][2]); tf32_split(a.w, xb[q][3], xs[q][3]);
+                if constexpr (PRECISE) {
+                    tf32_split(a.x, xb[q][0], xs[q][0]); tf32_split(a.y, xb[q][1], xs[q][1]);
+                    tf32_split(a.z, xb[q][2], xs[q][2]); tf32_split(a.w, xb[q][3], xs[q][3]);
+                } else {
+                    xb[q][0] = tf32_rna(a.x); xb[q][1] = tf32_rna(a.y); xb[q][2] = tf32_rna(a.z); xb[q][3] = tf32_rna(a.w);
+                }
             }
 #pragma unroll
             for (int j = 0; j < NT; ++j) {
                 const float4 wv = *reinterpret_cast<const float4*>(&s_w[(8 * j + g) * cs + 16 * c + 4 * t]);
+                if constexpr (PRECISE) {
                 uint32_t wb[4], ws[4];
                 tf32_split(wv.x, wb[0], ws[0]); tf32_split(wv.y, wb[1], ws[1]); tf32_split(wv.z, wb[2], ws[2]); tf32_split(wv.w, wb[3], ws[3]);
                 // step 0: columns 4t, 4t+1 ; step 1: columns 4t+2, 4t+3.  The tensor core adds into
@@ -125,6 +131,15 @@ __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict_
 #pragma unroll
                     for (int e = 0; e < 4; ++e) acc[m][j][e] += cm[e] + cc[e];
                 }
+                } else {   // single-pass TF32 (gradients: 1e-3 tolerance), accumulate in the tensor core
+                    const uint32_t wb[4] = {tf32_rna(wv.x), tf32_rna(wv.y), tf32_rna(wv.z), tf32_rna(wv.w)};
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        const int qa = 2 * m, qb = 2 * m + 1;
+                        mma_tf32(acc[m][j], xb[qa][0], xb[qb][0], xb[qa][1], xb[qb][1], wb[0], wb[1]);
+                        mma_tf32(acc[m][j], xb[qa][2], xb[qb][2], xb[qa][3], xb[qb][3], wb[2], wb[3]);
+                    }
+                }
             }
         }
     }
@@ -138,6 +153,7 @@ __global__ void __launch_bounds__(256) linear_in_kernel(const float* __restrict_
             if (ra < N) *reinterpret_cast<float2*>(y + ra * D + d) = make_float2(acc[m][j][0] + b0, acc[m][j][1] + b1);
             if (rb < N) *reinterpret_cast<float2*>(y + rb * D + d) = make_float2(acc[m][j][2] + b0, acc[m][j][3] + b1);
         }
+    }   // tile
 }
 
 // =======================================================================================
@@ -154,37 +170,58 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
     extern __shared__ float s_w[];  // [C][D + 4] tf32 bits, then bias [C]
     float* s_b = s_w + C * DS;
     for (int i = threadIdx.x; i < C; i += 256) s_b[i] = bias ? __ldg(bias + i) : 0.f;
-    for (int i = threadIdx.x; i < C * D; i += 256) {
-        int c, d;
-        if (w_is_dc) { d = i / C; c = i - d * C; } else { c = i / D; d = i - c * D; }
-        s_w[c * DS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+    if (w_is_dc) {
+        for (int i = threadIdx.x; i < C * D; i += 256) {
+            const int d = i / C, c = i - d * C;
+            s_w[c * DS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+        }
+    } else {   // [C][D]: rows are contiguous, D % 4 == 0
+        for (int i = threadIdx.x; i < C * (D / 4); i += 256) {
+            const int c = i / (D / 4), q = i - c * (D / 4);
+            const float4 v = __ldg(reinterpret_cast<const float4*>(w) + i);
+            *reinterpret_cast<float4*>(&s_w[c * DS + 4 * q]) = make_float4(__uint_as_float(tf32_rna(v.x)), __uint_as_float(tf32_rna(v.y)),
+                                                                            __uint_as_float(tf32_rna(v.z)), __uint_as_float(tf32_rna(v.w)));
+        }
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kLinRows + warp * 16 + g;
-    const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
-    uint32_t fa[KS][4];
+    // Column order inside a pair of n8 tiles is permuted so that a lane's two C fragments are four
+    // CONSECUTIVE output columns (one 16-byte store per row): MMA column n of the first tile is
+    // output column 4*(n/2) + n%2 of the 16-column group, of the second tile 4*(n/2) + 2 + n%2.
+    const int wrow = 4 * (g >> 1) + (g & 1);
+    // Persistent: the weight staging above is paid once per CTA.  Work unit = 16 rows x a quarter of
+    // the columns, dealt round-robin to all warps of the grid (fine enough to balance the last round).
+    const int cq = (C / 16 + 3) / 4;   // 16-column groups per unit
+    const int64_t units = ((N + 15) / 16) * 4;
+    for (int64_t u = static_cast<int64_t>(blockIdx.x) * 8 + warp; u < units; u += static_cast<int64_t>(gridDim.x) * 8) {
+        const int64_t r0 = (u >> 2) * 16 + g;
+        const int j0 = static_cast<int>(u & 3) * cq, j1 = min(C / 16, j0 + cq);
+        const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
+        uint32_t fa[KS][4];
 #pragma unroll
-    for (int s = 0; s < KS; ++s) {
-        fa[s][0] = tf32_rna(__ldg(a + ra * D + 8 * s + t));
-        fa[s][1] = tf32_rna(__ldg(a + rb * D + 8 * s + t));
-        fa[s][2] = tf32_rna(__ldg(a + ra * D + 8 * s + t + 4));
-        fa[s][3] = tf32_rna(__ldg(a + rb * D + 8 * s + t + 4));
-    }
-    float* ya = y + r0 * ldy + 2 * t;
-    float* yb = y + (r0 + 8) * ldy + 2 * t;
-    const bool oka = r0 < N, okb = r0 + 8 < N;
-#pragma unroll 4
-    for (int j = 0; j < C / 8; ++j) {
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        const float* wr = &s_w[(8 * j + g) * DS + t];
+        for (int s = 0; s < KS; ++s) {
+            fa[s][0] = tf32_rna(__ldg(a + ra * D + 8 * s + t));
+            fa[s][1] = tf32_rna(__ldg(a + rb * D + 8 * s + t));
+            fa[s][2] = tf32_rna(__ldg(a + ra * D + 8 * s + t + 4));
+            fa[s][3] = tf32_rna(__ldg(a + rb * D + 8 * s + t + 4));
+        }
+        float* ya = y + r0 * ldy + 4 * t;
+        float* yb = y + (r0 + 8) * ldy + 4 * t;
+        const bool oka = r0 < N, okb = r0 + 8 < N;
+#pragma unroll 2
+        for (int j = j0; j < j1; ++j) {
+            float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+            const float* w0 = &s_w[(16 * j + wrow) * DS + t];
+            const float* w1 = w0 + 2 * DS;
 #pragma unroll
-        for (int s = 0; s < KS; ++s)
-            mma_tf32(acc, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(wr[8 * s]), __float_as_uint(wr[8 * s + 4]));
-        const float2 bb = *reinterpret_cast<const float2*>(&s_b[8 * j + 2 * t]);
-        const float b0 = bb.x, b1 = bb.y;
-        if (oka) *reinterpret_cast<float2*>(ya + 8 * j) = make_float2(acc[0] + b0, acc[1] + b1);
-        if (okb) *reinterpret_cast<float2*>(yb + 8 * j) = make_float2(acc[2] + b0, acc[3] + b1);
+            for (int s = 0; s < KS; ++s) {
+                mma_tf32(acc0, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(w0[8 * s]), __float_as_uint(w0[8 * s + 4]));
+                mma_tf32(acc1, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(w1[8 * s]), __float_as_uint(w1[8 * s + 4]));
+            }
+            const float4 bb = *reinterpret_cast<const float4*>(&s_b[16 * j + 4 * t]);
+            if (oka) __stcs(reinterpret_cast<float4*>(ya + 16 * j), make_float4(acc0[0] + bb.x, acc0[1] + bb.y, acc1[0] + bb.z, acc1[1] + bb.w));
+            if (okb) __stcs(reinterpret_cast<float4*>(yb + 16 * j), make_float4(acc0[2] + bb.x, acc0[3] + bb.y, acc1[2] + bb.z, acc1[3] + bb.w));
+        }
     }
 }
 
