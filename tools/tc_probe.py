@@ -27,10 +27,13 @@ st = torch.cuda.current_stream().cuda_stream
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
 
+counter = torch.zeros(1, dtype=torch.int32, device=dev)
+
+
 def run(mode):
     keys.zero_(); scratch.zero_()
     _lib.check(lib.b200vq_scores_tc(z.data_ptr(), 0, D, N, D, image.data_ptr(), emb.data_ptr(), e2.data_ptr(), K, 0,
-                                    mode, 1, 1.0 / 0.03, 1, 4, 0, keys.data_ptr(), scratch.data_ptr(), None, st), "tc")
+                                    mode, 1, 1.0 / 0.03, 1, 4, 0, keys.data_ptr(), scratch.data_ptr(), counter.data_ptr(), st), "tc")
 
 
 def timeit(mode, reps=20):
@@ -56,6 +59,8 @@ def overhead(reps=20):
 
 
 print(f"D={D} K={K} N={N}  zeroing overhead {overhead():.1f} us")
+counter.zero_(); run(_lib.MODE_SAMPLE); torch.cuda.synchronize()
+print(f"sampler: {int(counter.item())} expanded groups = {int(counter.item()) / N:.1f} per row")
 for dbg in sys.argv[4].split(",") if len(sys.argv) > 4 else ["0", "2", "3", "64", "6"]:
     for sp in (os.environ.get("PROBE_SPLITS", "0").split(",")):
         os.environ["B200VQ_TC_DEBUG"] = dbg

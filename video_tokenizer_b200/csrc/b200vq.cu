@@ -261,6 +261,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
     prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = scratch;
     prm.debug = 0;
+    prm.n_events = mode == B200VQ_MODE_SAMPLE ? n_resolved : nullptr;
     if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
     int rc = B200VQ_OK;

@@ -32,7 +32,7 @@ namespace b200vq {
 constexpr int kTcRows = 128;       // token rows per CTA (UMMA M)
 constexpr int kTcCodes = 256;      // codes per tile (UMMA N)
 constexpr int kTcBufs = 2;         // TMEM accumulator buffers (2 x 256 columns)
-constexpr int kTcStages = 4;       // codebook tiles in flight
+constexpr int kTcStages = 3;       // codebook tiles in flight
 constexpr int kTcEpiWarps = 16;    // 4 epilogue groups: group g drains columns [128*(g&1), +128) of buffer g>>1
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 3);  // + producer + 2 MMA issuers (one per accumulator buffer)
 constexpr float kTcMargin = 4e-5f; // ambiguity window on approximate scores (see header)

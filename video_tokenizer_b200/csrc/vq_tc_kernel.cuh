@@ -85,8 +85,8 @@ __device__ __forceinline__ float key_value(unsigned long long key) { return ord_
 constexpr uint32_t kOrdNegInf = 0x007FFFFFu;                       // orderable(-inf)
 constexpr unsigned long long kKeyNegInf = 0x007FFFFFull << 32;     // (-inf, no code)
 
-constexpr int kQueueSlots = 64;   // per epilogue warp (ring); a push adds <= 32, a flush removes 32
-constexpr int kQueueWords = 12;   // 8 scores, group id, row | hi16 << 16, 2 pad (48-byte entries)
+constexpr int kQueueSlots = 128;  // per epilogue warp (ring): <= 31 left over + 64 pushed between two drain checks
+constexpr int kQueueWords = 10;   // 8 scores (q_sc) + group id, row | hi16 << 16 (q_meta)
 
 struct TcParams {
     const void* z;
@@ -103,60 +103,21 @@ struct TcParams {
     unsigned long long* keys; // (N) merged with atomicMax
     float* second;            // (N) deterministic modes: runner-up approximate score (orderable bits, atomicMax)
     int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies, 64 = no events
-};
-
-// per-warp queue + per-row state shared by the epilogue warps of a CTA
-struct Epi {
-    float* queue;                 // this warp's ring
-    unsigned long long* s_key;    // (128) per-row best (value, code)
-    uint32_t* s_second;           // (128) per-row runner-up value, orderable bits (deterministic)
-    uint32_t* s_thr;              // (128) per-row largest group maximum pushed so far, orderable bits (deterministic)
-    uint32_t qhead, qtail;        // warp-uniform
-    uint32_t row_local, lane;
-    float thr;                    // lane's row: det = best - margin ; sample = 19.02 - vstar*log2(e)
-    // stochastic only
-    uint32_t grow0;               // global row id of local row 0
-    float t_inv;
-    uint64_t seed, offset;
-    uint32_t k_end_global;
+    unsigned int* n_events;   // nullable: += groups expanded by the sampler (statistics)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
 
-// ---- deterministic: merge one queued group into its row's (best, runner-up) -----------------------
-__device__ __noinline__ void det_flush(const float* queue, uint32_t qhead, uint32_t n, uint32_t lane,
-                                       unsigned long long* s_key, uint32_t* s_second) {
-    if (lane < n) {
-        const float* e = queue + ((qhead + lane) & (kQueueSlots - 1)) * kQueueWords;
-        const float4 s0 = *reinterpret_cast<const float4*>(e);
-        const float4 s1 = *reinterpret_cast<const float4*>(e + 4);
-        const uint2 meta = *reinterpret_cast<const uint2*>(e + 8);
-        const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-        float best = -INFINITY, sec = -INFINITY;
-        uint32_t bi = 0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            sec = fmaxf(sec, fminf(s[j], best));
-            if (s[j] > best) { best = s[j]; bi = j; }
-        }
-        const uint32_t rl = meta.y & 0xFFu;
-        const unsigned long long old = atomicMax(s_key + rl, make_key(best, meta.x * 8 + bi));
-        // the loser of every key comparison is a runner-up candidate
-        const float runner = fmaxf(sec, fminf(key_value(old), best));
-        atomicMax(s_second + rl, orderable(runner));
-    }
-    __syncwarp();
-}
-
-// ---- stochastic: expand one queued group (its 8 Gumbels) and merge its best perturbed score -------
-__device__ __noinline__ void sample_flush(const float* queue, uint32_t qhead, uint32_t n, uint32_t lane,
+// ---- stochastic: expand up to 32 queued groups, one per lane (the 8 Gumbels of the group), and merge
+// each one's best perturbed score into its row's key ---------------------------------------------------
+__device__ __noinline__ void sample_flush(const float* q_sc, const uint2* q_meta, uint32_t qhead, uint32_t n, uint32_t lane,
                                           unsigned long long* s_key, uint32_t grow0, float t_inv, uint64_t seed,
                                           uint64_t offset, uint32_t k_end_global) {
     if (lane < n) {
-        const float* e = queue + ((qhead + lane) & (kQueueSlots - 1)) * kQueueWords;
-        const float4 s0 = *reinterpret_cast<const float4*>(e);
-        const float4 s1 = *reinterpret_cast<const float4*>(e + 4);
-        const uint2 meta = *reinterpret_cast<const uint2*>(e + 8);
+        const uint32_t slot = (qhead + lane) & (kQueueSlots - 1);
+        const float4 s0 = *reinterpret_cast<const float4*>(q_sc + slot * 8);
+        const float4 s1 = *reinterpret_cast<const float4*>(q_sc + slot * 8 + 4);
+        const uint2 meta = q_meta[slot];
         const uint32_t group = meta.x, rl = meta.y & 0xFFu, hi16 = meta.y >> 16;
         float g[8];
         group_noise(group, grow0 + rl, seed, offset, hi16, g);
@@ -173,37 +134,11 @@ __device__ __noinline__ void sample_flush(const float* queue, uint32_t qhead, ui
     __syncwarp();
 }
 
-template <bool SAMPLE>
-__device__ __forceinline__ void epi_flush(Epi& c, uint32_t n) {
-    if (SAMPLE) {
-        sample_flush(c.queue, c.qhead, n, c.lane, c.s_key, c.grow0, c.t_inv, c.seed, c.offset, c.k_end_global);
-        c.thr = fmaf(key_value(c.s_key[c.row_local]), -kLog2e, 19.02f);
-    } else {
-        det_flush(c.queue, c.qhead, n, c.lane, c.s_key, c.s_second);
-    }
-    c.qhead += n;
+__device__ __forceinline__ float lg2_approx(float x) {
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
-
-// push the groups flagged in this warp (ballot b) and drain the queue when 32 are waiting
-template <bool SAMPLE>
-__device__ __forceinline__ void epi_push(Epi& c, uint32_t b, bool ev, const uint32_t* v8, uint32_t group, uint32_t hi16,
-                                         float m) {
-    if (ev) {
-        if (!SAMPLE) {   // the group maximum is a lower bound of the row's best: later groups must beat it
-            c.thr = fmaxf(c.thr, m - kTcMargin);
-            atomicMax(c.s_thr + c.row_local, orderable(m));
-        }
-        const uint32_t slot = (c.qtail + __popc(b & ((1u << c.lane) - 1u))) & (kQueueSlots - 1);
-        float* e = c.queue + slot * kQueueWords;
-        *reinterpret_cast<uint4*>(e) = make_uint4(v8[0], v8[1], v8[2], v8[3]);
-        *reinterpret_cast<uint4*>(e + 4) = make_uint4(v8[4], v8[5], v8[6], v8[7]);
-        *reinterpret_cast<uint2*>(e + 8) = make_uint2(group, c.row_local | (hi16 << 16));
-    }
-    c.qtail += __popc(b);
-    __syncwarp();
-    if (c.qtail - c.qhead >= 32u) epi_flush<SAMPLE>(c, 32u);
-}
-
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -216,7 +151,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
     return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_a_chunks(D) * 16 + kTcStages * tc_tile_bytes(D) +
-           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + 2 * kTcRows * 4 + 256;
+           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + 2 * kTcRows * 4 + 512;
 }
 
 template <int D, typename T, int MODE>
@@ -237,6 +172,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     uint32_t* s_thr = s_second + kTcRows;
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_thr + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 2 * kTcBufs);
+    uint32_t* s_qtail = s_tmem + 4;   // (kTcEpiWarps) queue tails of the sampling epilogue
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kTcRows;
@@ -268,6 +204,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         s_key[threadIdx.x] = make_key(-INFINITY, first_code);
         s_second[threadIdx.x] = kOrdNegInf;
         s_thr[threadIdx.x] = kOrdNegInf;
+        if (threadIdx.x < kTcEpiWarps) s_qtail[threadIdx.x] = 0u;
     } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTcStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -371,34 +308,82 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                 }
             }
         } else {
-        Epi c;
-        c.queue = s_queue + warp * kQueueSlots * kQueueWords;
-        c.s_key = s_key;
-        c.s_second = s_second;
-        c.s_thr = s_thr;
-        c.qhead = c.qtail = 0;
-        c.row_local = 32 * (warp & 3) + lane;
-        c.lane = lane;
-        c.thr = SAMPLE ? INFINITY : -INFINITY;   // "everything can matter" until the first flush
-        c.grow0 = static_cast<uint32_t>(p.row_offset + row0);
-        c.t_inv = p.t_inv;
-        c.seed = p.seed;
-        c.offset = p.offset;
-        c.k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
+        // ---- stochastic mode: lazy Gumbel-max.  Per group of 8 codes a few branch-free instructions decide
+        // whether the group's bound (its largest score + the largest Gumbel its 16 head bits allow) can beat
+        // the row's best perturbed score so far.  Such groups are rare after the first tiles and rows of a
+        // warp hit them at different times, so a lane only QUEUES them (8 scores + ids into the warp's
+        // shared-memory ring, slot from a shared-memory atomic); whenever 32 are waiting the warp expands
+        // them one per lane with all lanes busy (sample_flush).
+        const uint32_t row_local = 32 * (warp & 3) + lane;
+        float* q_sc = s_queue + warp * (kQueueSlots * kQueueWords);
+        uint2* q_meta = reinterpret_cast<uint2*>(q_sc + kQueueSlots * 8);
+        uint32_t* q_tail = s_qtail + warp;
+        uint32_t qhead = 0;
+        const uint32_t grow0 = static_cast<uint32_t>(p.row_offset + row0);
+        const uint32_t k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
         const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
         const float tl2e = p.t_inv * kLog2e;
-        uint32_t v[32];
+        float thr = INFINITY;   // 19.02 - vstar * log2(e); "everything can matter" until a key exists
+        uint32_t va[32];
+        float lh[16];           // log2 of the tile's 16 group heads
+        uint32_t group0 = 0;
+        // one chunk of 32 columns: 4 group tests, queue the candidates, drain when 32 are waiting
+        auto process = [&](uint32_t (&v)[32], const int ch, const int valid) {
+            thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);   // all four epilogue groups' progress
+            if ((ch + 1) * 32 > valid) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (ch * 32 + j >= valid) v[j] = 0xFF800000u;
+            }
+            uint32_t evmask = 0;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                evmask |= fmaf(max8(&v[8 * g]), tl2e, thr) > lh[4 * ch + g] ? (1u << g) : 0u;
+            }
+            if (__any_sync(0xffffffffu, evmask != 0u) && !(p.debug & 64)) {
+#pragma unroll
+                for (int hg = 0; hg < 2; ++hg) {   // two groups, then a drain check: the ring never overflows
+#pragma unroll
+                    for (int gg = 0; gg < 2; ++gg) {
+                        const int g = 2 * hg + gg;
+                        if (evmask & (1u << g)) {
+                            const uint32_t slot = atomicAdd(q_tail, 1u) & (kQueueSlots - 1);
+                            float* e = q_sc + slot * 8;
+                            *reinterpret_cast<uint4*>(e) = make_uint4(v[8 * g], v[8 * g + 1], v[8 * g + 2], v[8 * g + 3]);
+                            *reinterpret_cast<uint4*>(e + 4) = make_uint4(v[8 * g + 4], v[8 * g + 5], v[8 * g + 6], v[8 * g + 7]);
+                            // the head back from its log2 (exact: |2^lg2(h) - h| << 0.5 for h < 2^16)
+                            q_meta[slot] = make_uint2(group0 + 4 * ch + g,
+                                                      row_local | (__float2uint_rn(ex2_approx(lh[4 * ch + g])) << 16));
+                        }
+                    }
+                    __syncwarp();
+                    // Drain inside the tile only when the ring could overflow (the next two groups add <= 64):
+                    // while this warp expands groups its half of the accumulator is not released and the
+                    // MMAs of the buffer wait.  The regular drain is at the end of the tile, after the release.
+                    uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead;
+                    if (pending > kQueueSlots - 64u) {
+                        do {
+                            sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
+                            qhead += 32u;
+                            pending -= 32u;
+                        } while (pending >= 32u);
+                        thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);
+                    }
+                }
+            }
+        };
         for (int i = buf; i < ntiles; i += kTcBufs) {
             const int64_t code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes + half * 128;  // index within the image
-            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);            // multiple of 16
+            group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);                           // multiple of 16
             const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
-            Philox4 r0, r1;
-            if (SAMPLE) {   // 16 random bits per group, two Philox calls per tile, before the accumulator is needed
-                r0 = group_head_words(group0 >> 3, c.grow0 + c.row_local, p.seed, p.offset);
-                r1 = group_head_words((group0 >> 3) + 1, c.grow0 + c.row_local, p.seed, p.offset);
-                c.thr = fmaf(key_value(s_key[c.row_local]), -kLog2e, 19.02f);      // other groups' progress
-            } else {
-                c.thr = fmaxf(c.thr, ord_value(s_thr[c.row_local]) - kTcMargin);
+            // Before the accumulator is needed: 16 random bits per group (two Philox calls per tile) and
+            // their log2, so that the in-loop test   head < 2^(m * tl2e + thr)   is   m * tl2e + thr > log2(head)
+            // (one FFMA + one compare); head 0 -> -inf: always a candidate.
+            {
+                const Philox4 r0 = group_head_words(group0 >> 3, grow0 + row_local, p.seed, p.offset);
+                const Philox4 r1 = group_head_words((group0 >> 3) + 1, grow0 + row_local, p.seed, p.offset);
+#pragma unroll
+                for (int g = 0; g < 16; ++g)
+                    lh[g] = lg2_approx(__uint_as_float(0x4B000000u | head_hi16(g < 8 ? r0 : r1, g & 7)) - 8388608.0f);
             }
             mbar_wait(bar_tfull + 8 * buf, (i / kTcBufs) & 1);
             tc_fence_after();
@@ -406,63 +391,34 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
 #pragma unroll
             for (int ch = 0; ch < 4; ++ch) {
-                tmem_ld32(t_lane + ch * 32, v);
-                if (SAMPLE && ch > 0) c.thr = fmaf(key_value(s_key[c.row_local]), -kLog2e, 19.02f);
-                tmem_ld_wait32(v);
+                tmem_ld32(t_lane + ch * 32, va);
+                tmem_ld_wait32(va);
                 if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
                     tc_fence_before();
                     mbar_arrive(bar_tempty + 8 * buf);
                 }
-                if ((ch + 1) * 32 > valid) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) if (ch * 32 + j >= valid) v[j] = 0xFF800000u;
-                }
-                // 4 groups: all maxima and tests first (independent), one vote for the rare path
-                float m[4];
-                uint32_t evmask = 0;
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    m[g] = max8(&v[8 * g]);
-                    bool ev;
-                    if (SAMPLE) {
-                        const uint32_t h = head_hi16(ch < 2 ? r0 : r1, 4 * (ch & 1) + g);
-                        const float fh = __uint_as_float(0x4B000000u | h) - 8388608.0f;
-                        ev = fh < ex2_approx(fmaf(m[g], tl2e, c.thr));
-                    } else {
-                        ev = m[g] > c.thr;
-                    }
-                    evmask |= ev ? (1u << g) : 0u;
-                }
-                const uint32_t um = __reduce_or_sync(0xffffffffu, evmask);
-                if (um != 0u && !(p.debug & 64)) {
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        if (um & (1u << g)) {
-                            // re-test against the threshold the lane may have raised while pushing earlier groups
-                            const bool ev = ((evmask >> g) & 1u) && (SAMPLE || m[g] > c.thr);
-                            const uint32_t b = __ballot_sync(0xffffffffu, ev);
-                            if (b) epi_push<SAMPLE>(c, b, ev, &v[8 * g], group0 + 4 * ch + g,
-                                                    SAMPLE ? head_hi16(ch < 2 ? r0 : r1, 4 * (ch & 1) + g) : 0u, m[g]);
-                        }
-                    }
-                }
+                process(va, ch, valid);
+            }
+            // regular drain, off the accumulator's critical path
+            __syncwarp();
+            for (uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead; pending >= 32u; pending -= 32u) {
+                sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
+                qhead += 32u;
             }
         }
-        while (c.qtail != c.qhead) epi_flush<SAMPLE>(c, min(32u, c.qtail - c.qhead));
+        __syncwarp();
+        for (uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead; pending != 0u;) {
+            const uint32_t n = min(32u, pending);
+            sample_flush(q_sc, q_meta, qhead, n, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
+            qhead += n;
+            pending -= n;
+        }
+        if (p.n_events && lane == 0) atomicAdd(p.n_events, qhead);
         // all four groups done -> publish the rows (named barrier over the 512 epilogue threads)
         asm volatile("bar.sync 1, 512;" ::: "memory");
         if (grp == 0) {
-            const int64_t row = row0 + c.row_local;
-            if (row < p.N && ntiles > 0) {
-                const unsigned long long mine = s_key[c.row_local];
-                const unsigned long long old = atomicMax(p.keys + row, mine);
-                if (!SAMPLE) {
-                    // cross-split merge: the loser of every key comparison is a runner-up candidate
-                    float runner = ord_value(s_second[c.row_local]);
-                    if (old != 0ull) runner = fmaxf(runner, fminf(key_value(old), key_value(mine)));
-                    atomicMax(reinterpret_cast<unsigned int*>(p.second) + row, orderable(runner));
-                }
-            }
+            const int64_t row = row0 + row_local;
+            if (row < p.N && ntiles > 0) atomicMax(p.keys + row, s_key[row_local]);
         }
         }  // SAMPLE
     }
