@@ -181,3 +181,31 @@ def test_token_sharded_sync_one_collective_semantics():
         assert torch.allclose(y0, (x0 + x1) / 2) and torch.equal(y0, y1)
     for i in range(2):
         assert torch.equal(u0[i], h0[i] + h1[i]) and torch.equal(u0[i], u1[i])
+
+
+def _sync_flat(rank, world):
+    """parameter grads handed out as views of one flat buffer + (2, K) histograms: the fast path"""
+    torch.manual_seed(0)
+    m = _FakeBottleneck(rank)
+    g = torch.Generator().manual_seed(20 + rank)
+    ps = list(m.parameters())
+    flat = torch.randn(sum(p.numel() for p in ps) + 3, generator=g)
+    off = 0
+    for p in ps:
+        p.grad = flat[off:off + p.numel()].view(p.shape)
+        off += p.numel()
+    hists = torch.randint(0, 99, (2, 32), generator=g, dtype=torch.int32)
+    m.regularizer.last_usage = (hists[1], hists[0])
+    before = [p.grad.clone() for p in ps]
+    hb = hists.clone()
+    usage = sharded.token_sharded_sync(m)
+    return before, [p.grad.clone() for p in ps], hb, torch.stack([usage[1], usage[0]]).clone()
+
+
+def test_token_sharded_sync_flat_buffer_fast_path():
+    out = _run(_sync_flat)
+    b0, a0, h0, u0 = out[0]
+    b1, a1, h1, u1 = out[1]
+    for x0, x1, y0, y1 in zip(b0, b1, a0, a1):
+        assert torch.allclose(y0, (x0 + x1) / 2) and torch.equal(y0, y1)
+    assert torch.equal(u0, h0 + h1) and torch.equal(u0, u1)

@@ -349,6 +349,16 @@ def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Ten
     return out
 
 
+# device index -> (flat gradient buffer, number of gradient floats, (2, K) int32 histograms) of the last
+# one-call backward, for sharded.token_sharded_sync
+LAST_FLAT: dict = {}
+
+
+def _dist_world() -> int:
+    import torch.distributed as dist
+    return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
 class _BottleneckFunction(torch.autograd.Function):
     """Whole Bottleneck step (in_linear -> quantizer -> out_linear + usage statistics) in ONE host
     call per direction: b200vq_bottleneck_forward / b200vq_bottleneck_backward.
@@ -386,6 +396,7 @@ class _BottleneckFunction(torch.autograd.Function):
             _lib.check(rc, "b200vq_bottleneck_forward")
         ctx.save_for_backward(x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste)
         ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
+        ctx.hists = hists
         ctx.mark_non_differentiable(idx, hists, usage)
         return out, z, znorm, emb, ste, idx, losses, hists, usage
 
@@ -408,11 +419,27 @@ class _BottleneckFunction(torch.autograd.Function):
         with torch.cuda.device(dev):
             xx, ldx, _ = _rows2d(x.detach())
             gx = torch.empty(x.shape, **f32) if need[0] else None
-            gw_in = torch.empty(D, C, **f32) if need[1] else None
-            gb_in = torch.empty(D, **f32) if (has_b_in and need[2]) else None
-            gw = torch.empty(K, D, **f32) if need[3] else None
-            gw_out = torch.empty(C, D, **f32) if (need[4] or (has_b_out and need[5])) else None
-            gb_out = torch.empty(C, **f32) if (has_b_out and need[5]) else None
+            # every parameter gradient is a view of ONE flat buffer [codebook | W_in | b_in | W_out | b_out]
+            # (16-byte aligned pieces), so a token-sharded job all-reduces them with one collective and no
+            # packing copies (sharded.token_sharded_sync)
+            sizes = [K * D, D * C, D, C * D, C]
+            offs, tot = [], 0
+            for n in sizes:
+                offs.append(tot)
+                tot += (n + 3) // 4 * 4
+            sync = _dist_world() > 1
+            hists = ctx.hists if sync else None
+            flat = torch.empty(tot + (hists.numel() if sync else 0), **f32)
+            if sync:   # usage histograms ride in the same collective (counts are exact in fp32 below 2^24)
+                flat[tot:].copy_(hists.view(-1))
+                LAST_FLAT[dev.index] = (flat, tot, hists)
+            gw = flat[offs[0]:offs[0] + sizes[0]].view(K, D) if need[3] else None
+            gw_in = flat[offs[1]:offs[1] + sizes[1]].view(D, C) if need[1] else None
+            gb_in = flat[offs[2]:offs[2] + sizes[2]] if (has_b_in and need[2]) else None
+            gw_out = flat[offs[3]:offs[3] + sizes[3]].view(C, D) if (need[4] or (has_b_out and need[5])) else None
+            gb_out = flat[offs[4]:offs[4] + sizes[4]] if (has_b_out and need[5]) else None
+            if tot != sum(sizes) or any(t is None for t in (gw, gw_in, gb_in, gw_out, gb_out)):
+                flat[:tot].zero_()   # padding / unused pieces must not carry garbage into the all-reduce
             ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
             rc = lib.b200vq_bottleneck_backward(
                 _ptr(go), ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,

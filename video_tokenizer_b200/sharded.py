@@ -75,6 +75,25 @@ def fused_allreduce(tensors: Sequence[torch.Tensor], average: Sequence[bool], gr
         off += n
 
 
+def _same_storage(a: torch.Tensor, b: torch.Tensor) -> bool:
+    return a.untyped_storage().data_ptr() == b.untyped_storage().data_ptr()
+
+
+def _flat_of(grads: Sequence[torch.Tensor]):
+    """(flat, n_grad_floats, hists or None) if every gradient aliases one flat fp32 buffer, else (None, 0, None)."""
+    g0 = grads[0]
+    if g0.is_cuda:
+        from . import functional as VF
+        packed = VF.LAST_FLAT.get(g0.device.index)
+        if packed is not None and all(_same_storage(g, packed[0]) for g in grads):
+            return packed
+    base = g0._base
+    if (base is not None and base.dim() == 1 and base.is_contiguous() and base.dtype == torch.float32
+            and all(g._base is base for g in grads)):
+        return base, base.numel(), None
+    return None, 0, None
+
+
 def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
     """After loss.backward() on every rank: average the bottleneck's parameter grads and sum
     the fused usage histograms across ranks in ONE collective.  Returns the global
@@ -83,6 +102,25 @@ def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, t
     tensors: List[torch.Tensor] = [p.grad for p in params]
     flags = [True] * len(tensors)
     usage = getattr(getattr(bottleneck, "regularizer", None), "last_usage", None)
+    # fast path: the one-call backward hands out every parameter gradient as a piece of one flat buffer
+    # (autograd keeps the storage, so p.grad aliases it): ONE collective over [grads | histograms as fp32]
+    if tensors and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        world = dist.get_world_size(group)
+        flat, tot, hists = _flat_of(tensors)
+        if flat is not None:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+            if hists is not None and usage is not None and _same_storage(usage[0], hists):
+                hists.view(-1).copy_(flat[tot:])
+                flat[:tot].div_(world)
+                return usage
+            flat.div_(world)
+            if usage is not None:
+                hf, hb = usage
+                if _same_storage(hf, hb) and hf._base is not None and hf._base.is_contiguous():
+                    dist.all_reduce(hf._base, op=dist.ReduceOp.SUM, group=group)   # (2, K) int32: one more small collective
+                else:
+                    fused_allreduce([hf, hb], [False, False], group)
+            return usage
     if usage is not None:
         hf, hb = usage
         if int(hb.numel()) and dist.is_initialized():
@@ -110,3 +148,98 @@ def codebook_sharded_select(score_slice: Callable[[int, int], torch.Tensor],
     if world > 1:
         dist.all_reduce(rows, op=dist.ReduceOp.SUM, group=group)
     return keys, key_indices(keys), rows
+
+
+# ---- codebook-sharded quantizer on the device (C ABI + NCCL) ----------------------------------
+class _CodebookShardedVQ(torch.autograd.Function):
+    """Quantizer step with the codebook rows [k_begin, k_begin + K_local) on this rank and the tokens
+    replicated: local scores -> all-reduce(MAX) of the packed keys -> owner-only
+    rows all-reduce(SUM) -> finish.  The backward scatter-adds owned rows only, so the codebook
+    gradient needs no collective; grad_z is identical on every rank."""
+
+    @staticmethod
+    def forward(ctx, z, weight_local, cfg):
+        from . import _lib, functional as VF
+        K, k_begin, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset, group = cfg
+        ctx.set_materialize_grads(False)
+        lib = _lib.load()
+        dev = z.device
+        D = z.shape[-1]
+        K_local = weight_local.shape[0]
+        zz, stride = VF.rows_view(z.detach())
+        N = zz.shape[:-1].numel()
+        st = VF._stream
+        f32 = dict(dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            emb_l, e2_l, wnorm_l = VF.prepare_codebook(weight_local, l2norm)
+            keys = torch.zeros(N, dtype=torch.int64, device=dev)
+            use_tc = VF.SCORING == "tc" and lib.b200vq_tc_supported(D, int(l2norm), mode) and k_begin % 256 == 0
+            if use_tc:
+                image = VF.prepare_codebook_tc(emb_l)
+                scratch = torch.zeros(lib.b200vq_tc_scratch_bytes(N) // 4 + 4, **f32)
+                _lib.check(lib.b200vq_scores_tc(zz.data_ptr(), VF._DTYPES[zz.dtype], stride, N, D, image.data_ptr(),
+                                                emb_l.data_ptr(), e2_l.data_ptr(), K_local, k_begin, mode, int(l2norm),
+                                                t_inv, seed, offset, 0, keys.data_ptr(), scratch.data_ptr(), None, st()),
+                           "b200vq_scores_tc")
+            else:
+                _lib.check(lib.b200vq_scores_partial(zz.data_ptr(), VF._DTYPES[zz.dtype], stride, N, D, emb_l.data_ptr(),
+                                                     e2_l.data_ptr(), K_local, k_begin, mode, int(l2norm), t_inv, seed,
+                                                     offset, 0, keys.data_ptr(), st()), "b200vq_scores_partial")
+            allreduce_max_keys(keys, group)                                   # the cross-GPU max-loc
+            rows = torch.empty(N, D, **f32)
+            _lib.check(lib.b200vq_gather_owned(keys.data_ptr(), N, emb_l.data_ptr(), K_local, k_begin, D, rows.data_ptr(),
+                                               st()), "b200vq_gather_owned")
+            if dist.is_initialized() and dist.get_world_size(group) > 1:
+                dist.all_reduce(rows, op=dist.ReduceOp.SUM, group=group)      # only the owner wrote non-zero
+            znorm = torch.empty(*z.shape, **f32)
+            ste = torch.empty(*z.shape, **f32)
+            idx = torch.empty(N, dtype=torch.int64, device=dev)
+            zlen = torch.empty(N, **f32)
+            hists = torch.zeros(2, K, dtype=torch.int32, device=dev)
+            sqerr = torch.zeros(2, dtype=torch.float64, device=dev)
+            losses = torch.empty(3, **f32)
+            _lib.check(lib.b200vq_finish(zz.data_ptr(), VF._DTYPES[zz.dtype], stride, N, D, None, K, keys.data_ptr(),
+                                         rows.data_ptr(), int(l2norm), n_first, znorm.data_ptr(), ste.data_ptr(),
+                                         idx.data_ptr(), zlen.data_ptr(), hists[0].data_ptr(), hists[1].data_ptr(),
+                                         sqerr.data_ptr(), 1, N, beta, w_cb, losses.data_ptr(), st()), "b200vq_finish")
+        ctx.save_for_backward(znorm, zlen, idx, emb_l, wnorm_l, rows)
+        ctx.cfg = (bool(l2norm), beta, w_cb, N, D, K_local, k_begin, z.dtype, tuple(z.shape))
+        ctx.mark_non_differentiable(idx, hists)
+        return znorm, ste, idx, losses, hists
+
+    @staticmethod
+    def backward(ctx, g_znorm, g_ste, _gi, g_losses, _gh):
+        from . import _lib, functional as VF
+        znorm, zlen, idx, emb_l, wnorm_l, rows = ctx.saved_tensors
+        l2norm, beta, w_cb, N, D, K_local, k_begin, z_dtype, z_shape = ctx.cfg
+        lib = _lib.load()
+        dev = znorm.device
+
+        def _f32c(t):
+            return None if t is None else t.to(torch.float32).contiguous()
+
+        g_znorm, g_ste, g_losses = _f32c(g_znorm), _f32c(g_ste), _f32c(g_losses)
+        with torch.cuda.device(dev):
+            gz = torch.empty(z_shape, dtype=z_dtype, device=dev)
+            grad_emb = torch.empty(K_local, D, dtype=torch.float32, device=dev)
+            _lib.check(lib.b200vq_backward(VF._ptr(g_ste), VF._ptr(g_znorm), VF._ptr(g_losses), znorm.data_ptr(),
+                                           zlen.data_ptr(), idx.data_ptr(), emb_l.data_ptr(), rows.data_ptr(), k_begin, N, D,
+                                           K_local, int(l2norm), N, beta, w_cb, gz.data_ptr(), VF._DTYPES[z_dtype],
+                                           grad_emb.data_ptr(), VF._stream()), "b200vq_backward")
+            gw = torch.empty(K_local, D, dtype=torch.float32, device=dev)
+            _lib.check(lib.b200vq_codebook_backward(grad_emb.data_ptr(), None, emb_l.data_ptr(), wnorm_l.data_ptr(), K_local, D,
+                                                    int(l2norm), gw.data_ptr(), VF._stream()), "b200vq_codebook_backward")
+        return gz, gw, None
+
+
+def codebook_sharded_quantize(z, weight_local, K, k_begin, *, mode, l2norm, t_inv=1.0, beta=0.25, w_cb=1.0, n_first=None,
+                              seed=0, offset=0, group=None):
+    """Codebook-sharded quantizer step.  ``weight_local`` holds rows [k_begin, k_begin + K_local) of the
+    (K, D) codebook (``shard_bounds(K, world, rank, align=256)`` keeps the tensor-core path usable); z is
+    the same on every rank; in stochastic mode every rank must pass the same (seed, offset).
+    Returns (znorm, ste, idx (N,), losses (3), hists (2, K) int32 [batch, first instance])."""
+    if n_first is None:
+        n_first = z.shape[1] if z.dim() == 3 else z.shape[0]
+    cfg = (int(K), int(k_begin), int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed),
+           int(offset), group)
+    return _CodebookShardedVQ.apply(z, weight_local, cfg)
