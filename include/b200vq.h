@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 103
+#define B200VQ_VERSION 104
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -251,7 +251,9 @@ int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t 
  * that a training step costs two host calls instead of ~40.  fp32 x, b200vq_linear_supported(C, D).
  *   forward  outputs: z (N,D) 'projected_z'; emb (K,D) + wnorm (K) (saved for backward); znorm, ste (N,D);
  *            idx (N) int64; zlen (N); hist, hist_first (K) int32; losses (3); usage4 (4, nullable:
- *            index_usage, index_usage_batch, kl_uni, perplexity); out (N,C; row stride ldo) 'output'
+ *            index_usage, index_usage_batch, kl_uni, perplexity); norms2 (2, nullable: batch means of
+ *            |x[b,0,:]| and |x[b,n_first-1,:]|, the 'input_norm_first/last' diagnostics; rows of one sample
+ *            are the n_first consecutive rows); out (N,C; row stride ldo) 'output'
  *   backward inputs: g_out (N,C; ldg) grad of 'output' (nullable); g_losses (3, device, nullable);
  *            g_ste / g_znorm / g_z (N,D) and g_emb (K,D): extra grads on 'regularized_z',
  *            'unregularized_z', 'projected_z', 'emb' (all nullable); the tensors saved by forward
@@ -265,7 +267,8 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
                               int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
                               float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
-                              float* out, int64_t ldo, void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
+                              float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                              b200vq_stream_t stream);
 int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
                                const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
                                int64_t N, int C, const float* w_in, const float* w_out, const float* emb,

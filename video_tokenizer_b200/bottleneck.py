@@ -281,24 +281,28 @@ class Bottleneck(nn.Module):
         regularized_z = self.regularizer.decode(bottleneck_rep)
         return self.project_out(regularized_z)
 
-    def forward(self, x):
+    def _input_norms(self, x):
         with torch.no_grad():
-            input_norm_first = torch.linalg.vector_norm(x[:, 0, :].float(), dim=-1).mean()
-            input_norm_last = torch.linalg.vector_norm(x[:, -1, :].float(), dim=-1).mean()
-        if self.sync_diagnostics:
-            input_norm_first, input_norm_last = input_norm_first.item(), input_norm_last.item()
+            first = torch.linalg.vector_norm(x[:, 0, :].float(), dim=-1).mean()
+            last = torch.linalg.vector_norm(x[:, -1, :].float(), dim=-1).mean()
+        return (first.item(), last.item()) if self.sync_diagnostics else (first, last)
+
+    def forward(self, x):
         reg = self.regularizer
         if (self.norm is None and type(reg) is SimpleVectorQuantizer and reg.entropy_loss_weight == 0
                 and self.project_dim == self.bottleneck_dim and len(x.shape) == 3 and self.in_linear.bias is not None
                 and VF.bottleneck_supported(x, self.in_linear.weight, reg.embedding.weight, self.out_linear.weight)):
             # one host call per direction: in_linear -> quantizer -> out_linear (+ usage statistics)
             mode, t_inv, seed, offset = reg._step_config(x.device)
-            x_hat, projected_z, znorm, emb, ste, idx, losses, hists, usage = VF.bottleneck_step(
+            x_hat, projected_z, znorm, emb, ste, idx, losses, hists, usage, norms = VF.bottleneck_step(
                 x, self.in_linear.weight, self.in_linear.bias, reg.embedding.weight, self.out_linear.weight,
                 self.out_linear.bias, mode=mode, l2norm=reg.l2_normalized, t_inv=t_inv, beta=reg.beta,
                 w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset)
             regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, losses, hists[0], hists[1], usage)
             bottleneck_rep = regularized_output.pop("bottleneck_rep")
+            input_norm_first, input_norm_last = norms[0], norms[1]
+            if self.sync_diagnostics:
+                input_norm_first, input_norm_last = input_norm_first.item(), input_norm_last.item()
             return {
                 "output": x_hat,
                 "bottleneck_rep": bottleneck_rep,
@@ -307,6 +311,7 @@ class Bottleneck(nn.Module):
                 "input_norm_last": input_norm_last,
                 **regularized_output,
             }
+        input_norm_first, input_norm_last = self._input_norms(x)
         z = self.project_in(x)
         projected_z = z
         if self.regularizer is not None:

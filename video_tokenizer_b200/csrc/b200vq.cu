@@ -337,6 +337,9 @@ int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, i
     if (!z || (!emb && !q_rows) || !keys || !znorm_out || !ste_out || !idx_out || !zlen_out || !sqerr || z_row_stride < D)
         return B200VQ_EINVAL;
     if (finalize && (!losses || N_total <= 0)) return B200VQ_EINVAL;
+    if (specialised_dim(D) && ((reinterpret_cast<uintptr_t>(znorm_out) | reinterpret_cast<uintptr_t>(ste_out) |
+                                reinterpret_cast<uintptr_t>(emb) | reinterpret_cast<uintptr_t>(q_rows)) & 15))
+        return B200VQ_EALIGN;   // the dense fp32 tensors are accessed 16 bytes at a time
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const unsigned blocks = static_cast<unsigned>((N + 127) / 128);
     const unsigned long long* k64 = reinterpret_cast<const unsigned long long*>(keys);
@@ -402,6 +405,10 @@ int b200vq_backward(const float* g_ste, const float* g_znorm, const float* g_los
     if (rc) return rc;
     if (N == 0) return B200VQ_OK;
     if (!znorm || !zlen || !idx || (!emb && !q_rows) || !grad_z || k_offset < 0) return B200VQ_EINVAL;
+    if (specialised_dim(D) && ((reinterpret_cast<uintptr_t>(znorm) | reinterpret_cast<uintptr_t>(g_ste) |
+                                reinterpret_cast<uintptr_t>(g_znorm) | reinterpret_cast<uintptr_t>(emb) |
+                                reinterpret_cast<uintptr_t>(q_rows) | reinterpret_cast<uintptr_t>(grad_z)) & 15))
+        return B200VQ_EALIGN;   // the dense tensors are accessed 16 bytes at a time
     const unsigned blocks = static_cast<unsigned>((N + 127) / 128);
     if (specialised_dim(D)) {
         B200VQ_DISPATCH_DIM(D, DD, {
@@ -588,6 +595,27 @@ inline int add_inplace(float* dst, const float* src, int64_t n, cudaStream_t st)
     add_inplace_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(dst, src, n);
     return launch_check();
 }
+// mean over the batch of |x[b, 0, :]| and |x[b, n-1, :]| (Bottleneck.forward's diagnostics, bottleneck.py:171-172)
+__global__ void __launch_bounds__(128) input_norms_kernel(const float* __restrict__ x, int64_t ldx, int64_t n_tok, int C,
+                                                          int64_t B, float* __restrict__ out2) {
+    __shared__ float s_part[2][4];
+    const float* r0 = x + static_cast<int64_t>(blockIdx.x) * n_tok * ldx;
+    const float* r1 = r0 + (n_tok - 1) * ldx;
+    float a = 0.f, b = 0.f;
+    for (int c = threadIdx.x; c < C; c += 128) {
+        const float u = r0[c], v = r1[c];
+        a = fmaf(u, u, a);
+        b = fmaf(v, v, b);
+    }
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if ((threadIdx.x & 31) == 0) { s_part[0][threadIdx.x >> 5] = a; s_part[1][threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        const float t = s_part[threadIdx.x][0] + s_part[threadIdx.x][1] + s_part[threadIdx.x][2] + s_part[threadIdx.x][3];
+        atomicAdd(out2 + threadIdx.x, sqrtf(t) / static_cast<float>(B));
+    }
+}
 struct BnLayout {
     size_t e2, image, vq, ga, gz, gemb, total;
 };
@@ -618,7 +646,8 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
                               int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
                               float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
-                              float* out, int64_t ldo, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+                              float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                              b200vq_stream_t stream) {
     if (N <= 0 || K <= 0 || !valid_mode(mode)) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !weight || !w_out || !z || !emb || !wnorm || !znorm || !ste || !idx || !zlen || !hist || !hist_first ||
@@ -632,6 +661,12 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, true, st);
     if (rc) return rc;
+    if (norms2) {
+        if (n_first <= 0 || N % n_first) return B200VQ_EINVAL;
+        if ((rc = cuda_check(cudaMemsetAsync(norms2, 0, 2 * sizeof(float), st)))) return rc;
+        input_norms_kernel<<<static_cast<unsigned>(N / n_first), 128, 0, st>>>(x, ldx, n_first, C, N / n_first, norms2);
+        if ((rc = launch_check())) return rc;
+    }
     if ((rc = b200vq_prepare_codebook(weight, K, D, l2norm, emb, e2, wnorm, stream))) return rc;
     void* image = nullptr;
     if (use_tc && b200vq_tc_supported(D, l2norm, mode)) {

@@ -29,15 +29,22 @@ __global__ void __launch_bounds__(128) finish_kernel(const T* __restrict__ z, in
         uint32_t code = key_code(keys[row]);
         if (code >= K) code = 0;  // unreachable for valid keys; keeps the gather in bounds
         const float* q = q_rows ? q_rows + row * D : emb + static_cast<int64_t>(code) * D;
-        float* zo = znorm_out + row * D;
-        float* so = ste_out + row * D;
+        float4* zo = reinterpret_cast<float4*>(znorm_out + row * D);   // dense (N, D) fp32, D % 4 == 0: 16-byte accesses
+        float4* so = reinterpret_cast<float4*>(ste_out + row * D);
+        const float4* q4 = reinterpret_cast<const float4*>(q);
 #pragma unroll
-        for (int d = 0; d < D; ++d) {
-            const float qd = __ldg(q + d);
-            const float diff = __fsub_rn(qd, zn[d]);
-            zo[d] = zn[d];
-            so[d] = __fadd_rn(zn[d], diff);  // z + (q - z).detach()   (:307)
-            sq = fmaf(diff, diff, sq);
+        for (int d = 0; d < D; d += 4) {
+            const float4 qv = __ldg(q4 + d / 4);
+            const float qd[4] = {qv.x, qv.y, qv.z, qv.w};
+            float st[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float diff = __fsub_rn(qd[e], zn[d + e]);
+                st[e] = __fadd_rn(zn[d + e], diff);  // z + (q - z).detach()   (:307)
+                sq = fmaf(diff, diff, sq);
+            }
+            zo[d / 4] = make_float4(zn[d], zn[d + 1], zn[d + 2], zn[d + 3]);
+            so[d / 4] = make_float4(st[0], st[1], st[2], st[3]);
         }
         idx_out[row] = static_cast<int64_t>(code);
         zlen_out[row] = zlen;
@@ -68,6 +75,19 @@ __global__ void __launch_bounds__(128) finish_kernel(const T* __restrict__ z, in
     }
 }
 
+// four consecutive elements of a dense row (16-byte aligned for fp32, 8-byte for the half types)
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
+    *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float c, float d) {
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+    *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+}
+__device__ __forceinline__ void store4(__half* p, float a, float b, float c, float d) {
+    const __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+    *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+}
+
 // =======================================================================================
 // Backward.  One thread per row.  coef from device scalars so no host sync is needed.
 // =======================================================================================
@@ -91,16 +111,25 @@ __global__ void __launch_bounds__(128) backward_kernel(const float* __restrict__
     const float* q = q_rows ? q_rows + row * D : emb + (owned ? code : 0) * D;
     float zn[D], dzh[D];
     float proj = 0.f;
+    const float4* zn4 = reinterpret_cast<const float4*>(znorm + row * D);   // dense (N, D) fp32, D % 4 == 0
+    const float4* q4 = reinterpret_cast<const float4*>(q);
+    const float4* gs4 = reinterpret_cast<const float4*>(g_ste ? g_ste + row * D : nullptr);
+    const float4* gz4 = reinterpret_cast<const float4*>(g_zn ? g_zn + row * D : nullptr);
 #pragma unroll
-    for (int d = 0; d < D; ++d) {
-        zn[d] = znorm[row * D + d];
-        const float qd = __ldg(q + d);
-        float g = a * (zn[d] - qd);
-        if (g_ste) g += g_ste[row * D + d];
-        if (g_zn) g += g_zn[row * D + d];
-        dzh[d] = g;
-        proj = fmaf(zn[d], g, proj);
-        if (b != 0.f && owned) atomicAdd(grad_emb + code * D + d, b * (qd - zn[d]));
+    for (int d = 0; d < D; d += 4) {
+        const float4 zv = zn4[d / 4], qv = __ldg(q4 + d / 4);
+        float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g_ste) gv = gs4[d / 4];
+        if (g_zn) { const float4 t = gz4[d / 4]; gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w; }
+        const float zz[4] = {zv.x, zv.y, zv.z, zv.w}, qq[4] = {qv.x, qv.y, qv.z, qv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            zn[d + e] = zz[e];
+            const float g = a * (zz[e] - qq[e]) + gg[e];
+            dzh[d + e] = g;
+            proj = fmaf(zz[e], g, proj);
+            if (b != 0.f && owned) atomicAdd(grad_emb + code * D + d + e, b * (qq[e] - zz[e]));
+        }
     }
     GT* out = grad_z + row * D;
     if (l2norm) {
@@ -108,15 +137,14 @@ __global__ void __launch_bounds__(128) backward_kernel(const float* __restrict__
         if (len > kNormEps) {
             const float inv = 1.0f / len;
 #pragma unroll
-            for (int d = 0; d < D; ++d) out[d] = from_f32<GT>((dzh[d] - zn[d] * proj) * inv);
+            for (int d = 0; d < D; ++d) dzh[d] = (dzh[d] - zn[d] * proj) * inv;
         } else {
 #pragma unroll
-            for (int d = 0; d < D; ++d) out[d] = from_f32<GT>(dzh[d] * (1.0f / kNormEps));
+            for (int d = 0; d < D; ++d) dzh[d] = dzh[d] * (1.0f / kNormEps);
         }
-    } else {
-#pragma unroll
-        for (int d = 0; d < D; ++d) out[d] = from_f32<GT>(dzh[d]);
     }
+#pragma unroll
+    for (int d = 0; d < D; d += 4) store4(out + d, dzh[d], dzh[d + 1], dzh[d + 2], dzh[d + 3]);
 }
 
 // grad_weight = J_normalise^T (grad_emb + g_emb).  One warp per code row.

@@ -381,8 +381,9 @@ class _BottleneckFunction(torch.autograd.Function):
             nd = torch.empty(3, *lead, D, **f32)
             z, znorm, ste = nd[0], nd[1], nd[2]
             emb = torch.empty(K, D, **f32)
-            small = torch.empty(K + N + 8, **f32)           # wnorm | zlen | losses(3) usage(4)
+            small = torch.empty(K + N + 12, **f32)          # wnorm | zlen | losses(3) usage(4) input norms(2)
             wnorm, zlen, losses, usage = small[:K], small[K:K + N], small[K + N:K + N + 3], small[K + N + 3:K + N + 7]
+            norms = small[K + N + 8:K + N + 10]
             idx = torch.empty(N, dtype=torch.int64, device=dev)
             hists = torch.empty(2, K, dtype=torch.int32, device=dev)
             ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
@@ -391,17 +392,17 @@ class _BottleneckFunction(torch.autograd.Function):
                 xx.data_ptr(), ldx, N, C, w_in.data_ptr(), _ptr(b_in), weight.data_ptr(), K, D, w_out.data_ptr(), _ptr(b_out),
                 mode, int(l2norm), t_inv, seed, offset, n_first, beta, w_cb, use_tc, z.data_ptr(), emb.data_ptr(),
                 wnorm.data_ptr(), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(), hists[0].data_ptr(),
-                hists[1].data_ptr(), losses.data_ptr(), usage.data_ptr(), out.data_ptr(), C, ws.data_ptr(), ws.numel(),
+                hists[1].data_ptr(), losses.data_ptr(), usage.data_ptr(), norms.data_ptr(), out.data_ptr(), C, ws.data_ptr(), ws.numel(),
                 _stream())
             _lib.check(rc, "b200vq_bottleneck_forward")
         ctx.save_for_backward(x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste)
         ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
         ctx.hists = hists
-        ctx.mark_non_differentiable(idx, hists, usage)
-        return out, z, znorm, emb, ste, idx, losses, hists, usage
+        ctx.mark_non_differentiable(idx, hists, usage, norms)
+        return out, z, znorm, emb, ste, idx, losses, hists, usage, norms
 
     @staticmethod
-    def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_losses, _gh, _gu):
+    def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_losses, _gh, _gu, _gn):
         x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste = ctx.saved_tensors
         l2norm, beta, w_cb, N, C, D, K, has_b_in, has_b_out = ctx.cfg
         lib = _lib.load()
@@ -463,6 +464,6 @@ def bottleneck_supported(x, w_in, weight, w_out) -> bool:
 
 
 def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset):
-    """-> (output, projected_z, znorm, emb, ste, idx(N,), losses(3), hists(2,K) [batch, first], usage(4))"""
+    """-> (output, projected_z, znorm, emb, ste, idx(N,), losses(3), hists(2,K) [batch, first], usage(4), input norms(2))"""
     cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset))
     return _BottleneckFunction.apply(x, w_in, b_in, weight, w_out, b_out, cfg)
