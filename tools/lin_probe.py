@@ -1,0 +1,33 @@
+"""Tuning aid: time the streaming linear kernels alone (N=65536, C=768, D=24)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import video_tokenizer_b200 as V
+from video_tokenizer_b200 import _lib
+lib = V.load_library(); dev = torch.device("cuda")
+N, C, D = 65536, 768, 24
+xs = [torch.randn(N, C, device=dev) for _ in range(3)]     # rotate buffers: 3 x 201 MB > L2
+ys = [torch.empty(N, C, device=dev) for _ in range(3)]
+a = torch.randn(N, D, device=dev); w_in = torch.randn(D, C, device=dev) * 0.03; w_out = torch.randn(C, D, device=dev) * 0.1
+b_in = torch.zeros(D, device=dev); b_out = torch.zeros(C, device=dev)
+z = torch.empty(N, D, device=dev); dw = torch.empty(C, D, device=dev); cs = torch.empty(C, device=dev)
+st = torch.cuda.current_stream().cuda_stream
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+i = [0]
+def t(fn, reps=30):
+    for _ in range(3): fn()
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(reps): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps * 1e3
+def lin_in():
+    i[0] += 1; _lib.check(lib.b200vq_linear_in(xs[i[0] % 3].data_ptr(), C, N, C, w_in.data_ptr(), b_in.data_ptr(), D, z.data_ptr(), st), "in")
+def lin_out():
+    i[0] += 1; _lib.check(lib.b200vq_linear_out(a.data_ptr(), N, D, w_out.data_ptr(), 0, b_out.data_ptr(), C, ys[i[0] % 3].data_ptr(), C, st), "out")
+def lin_out_dc():
+    i[0] += 1; _lib.check(lib.b200vq_linear_out(a.data_ptr(), N, D, w_in.data_ptr(), 1, None, C, ys[i[0] % 3].data_ptr(), C, st), "out")
+def wgrad():
+    i[0] += 1; _lib.check(lib.b200vq_weight_grad(xs[i[0] % 3].data_ptr(), C, a.data_ptr(), N, C, D, dw.data_ptr(), 0, cs.data_ptr(), st), "wg")
+mb = N * C * 4 / 1e6
+for name, fn in (("linear_in(3xTF32)", lin_in), ("linear_out", lin_out), ("linear_out(dc)", lin_out_dc), ("weight_grad", wgrad)):
+    us = t(fn); print(f"{name:20s} {us:7.1f} us  {mb / us / 1e3 * 1e3 / 1e3:.2f} TB/s")

@@ -494,15 +494,15 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
         (reinterpret_cast<uintptr_t>(y) & 7))
         return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinInRows - 1) / kLinInRows, 2ll * sm_count()));
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinInRows - 1) / kLinInRows, static_cast<int64_t>(sm_count())));
     int rc = B200VQ_OK;
 #define B200VQ_LIN_IN(DD)                                                                        \
     if (precise) {                                                                               \
         if ((rc = set_smem(linear_in_kernel<DD, true>, smem))) return rc;                        \
-        linear_in_kernel<DD, true><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y);  \
+        linear_in_kernel<DD, true><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y);  \
     } else {                                                                                     \
         if ((rc = set_smem(linear_in_kernel<DD, false>, smem))) return rc;                       \
-        linear_in_kernel<DD, false><<<blocks, 256, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y); \
+        linear_in_kernel<DD, false><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y); \
     }
     switch (D) {
         case 8: B200VQ_LIN_IN(8); break;
@@ -527,12 +527,15 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
     if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & 15) || (reinterpret_cast<uintptr_t>(w) & 15)) return B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinRows - 1) / kLinRows, 2ll * sm_count()));
+    int lo_dbg = 0, lo_grid = 1;   // one 16-warp CTA per SM: the weight staging is paid once per SM
+    if (const char* env = std::getenv("B200VQ_LO_DEBUG")) lo_dbg = std::atoi(env);
+    if (const char* env = std::getenv("B200VQ_LO_GRID")) lo_grid = std::max(1, std::atoi(env));
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinRows - 1) / kLinRows, static_cast<int64_t>(lo_grid) * sm_count()));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
 #define B200VQ_LIN_OUT(DD)                                                           \
     if ((rc = set_smem(linear_out_kernel<DD>, smem))) return rc;                     \
-    linear_out_kernel<DD><<<blocks, 256, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy)
+    linear_out_kernel<DD><<<blocks, kLinOutThreads, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy, lo_dbg)
     switch (D) {
         case 8: B200VQ_LIN_OUT(8); break;
         case 16: B200VQ_LIN_OUT(16); break;

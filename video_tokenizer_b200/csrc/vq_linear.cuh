@@ -52,22 +52,23 @@ constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 // the MMA sees as k = t, t+4 of two consecutive k8 steps; w is read with the same mapping).
 // w lives in shared memory as fp32 (row stride C + 16 words: conflict-free LDS.128).
 // =======================================================================================
-constexpr int kLinInRows = 256;  // linear_in: 8 warps x 32 rows (two m16 tiles share every w fragment)
+constexpr int kLinInThreads = 512;                      // 16 warps share one staged weight matrix (1 CTA / SM)
+constexpr int kLinInRows = kLinInThreads;               // linear_in: 32 rows per warp (two m16 tiles share every w fragment)
 
 template <int D, bool PRECISE>
-__global__ void __launch_bounds__(256, 2) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
+__global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
                                                         const float* __restrict__ w, int w_is_cd,
                                                         const float* __restrict__ bias, float* __restrict__ y) {
     constexpr int NT = D / 8;
     extern __shared__ float s_w[];  // [D][C + 16]
     const int cs = C + 16;
     if (w_is_cd) {   // w given as [C][D] (out_linear.weight, for grad_a = grad_y W_out): transpose while staging
-        for (int i = threadIdx.x; i < C * D; i += 256) {
+        for (int i = threadIdx.x; i < C * D; i += kLinInThreads) {
             const int c = i / D, d = i - c * D;
             s_w[d * cs + c] = __ldg(w + i);
         }
     } else {
-        for (int i = threadIdx.x; i < D * (C / 4); i += 256) {
+        for (int i = threadIdx.x; i < D * (C / 4); i += kLinInThreads) {
             const int d = i / (C / 4), c4 = i - d * (C / 4);
             *reinterpret_cast<float4*>(&s_w[d * cs + 4 * c4]) = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(d) * C) + c4);
         }
@@ -162,21 +163,22 @@ __global__ void __launch_bounds__(256, 2) linear_in_kernel(const float* __restri
 // in_linear.weight, for grad_x = grad_z W_in).  It is kept in shared memory as TF32,
 // [C][D + 4] (conflict-free B fragments).  One warp = 16 rows x all C columns.
 // =======================================================================================
+constexpr int kLinOutThreads = 512;   // 16 warps share one staged weight matrix
 template <int D>
-__global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict__ a, int64_t N, const float* __restrict__ w,
+__global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float* __restrict__ a, int64_t N, const float* __restrict__ w,
                                                          int w_is_dc, const float* __restrict__ bias, int C,
-                                                         float* __restrict__ y, int64_t ldy) {
+                                                         float* __restrict__ y, int64_t ldy, int dbg) {
     constexpr int KS = D / 8, DS = D + 4;
     extern __shared__ float s_w[];  // [C][D + 4] tf32 bits, then bias [C]
     float* s_b = s_w + C * DS;
-    for (int i = threadIdx.x; i < C; i += 256) s_b[i] = bias ? __ldg(bias + i) : 0.f;
+    for (int i = threadIdx.x; i < C; i += kLinOutThreads) s_b[i] = bias ? __ldg(bias + i) : 0.f;
     if (w_is_dc) {
-        for (int i = threadIdx.x; i < C * D; i += 256) {
+        for (int i = threadIdx.x; i < C * D; i += kLinOutThreads) {
             const int d = i / C, c = i - d * C;
             s_w[c * DS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
         }
     } else {   // [C][D]: rows are contiguous, D % 4 == 0
-        for (int i = threadIdx.x; i < C * (D / 4); i += 256) {
+        for (int i = threadIdx.x; i < C * (D / 4); i += kLinOutThreads) {
             const int c = i / (D / 4), q = i - c * (D / 4);
             const float4 v = __ldg(reinterpret_cast<const float4*>(w) + i);
             *reinterpret_cast<float4*>(&s_w[c * DS + 4 * q]) = make_float4(__uint_as_float(tf32_rna(v.x)), __uint_as_float(tf32_rna(v.y)),
@@ -193,7 +195,8 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
     // the columns, dealt round-robin to all warps of the grid (fine enough to balance the last round).
     const int cq = (C / 16 + 3) / 4;   // 16-column groups per unit
     const int64_t units = ((N + 15) / 16) * 4;
-    for (int64_t u = static_cast<int64_t>(blockIdx.x) * 8 + warp; u < units; u += static_cast<int64_t>(gridDim.x) * 8) {
+    for (int64_t u = static_cast<int64_t>(blockIdx.x) * (kLinOutThreads / 32) + warp; u < units;
+         u += static_cast<int64_t>(gridDim.x) * (kLinOutThreads / 32)) {
         const int64_t r0 = (u >> 2) * 16 + g;
         const int j0 = static_cast<int>(u & 3) * cq, j1 = min(C / 16, j0 + cq);
         const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
@@ -215,6 +218,7 @@ __global__ void __launch_bounds__(256) linear_out_kernel(const float* __restrict
             const float* w1 = w0 + 2 * DS;
 #pragma unroll
             for (int s = 0; s < KS; ++s) {
+                if (dbg & 1) { acc0[0] += __uint_as_float(fa[s][0]); acc1[0] += __uint_as_float(fa[s][1]); continue; }
                 mma_tf32(acc0, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(w0[8 * s]), __float_as_uint(w0[8 * s + 4]));
                 mma_tf32(acc1, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(w1[8 * s]), __float_as_uint(w1[8 * s + 4]));
             }
