@@ -360,9 +360,17 @@ def run_b200(args):
     alg_bytes = N * (4 * D + 8) + K * kc * 2
     tc_tflops_issued = 2.0 * K * kc * N / (tc_ms * 1e-3) / 1e12
     fma_peak = 148 * 128 * 2 * 1.965e9 / 1e12
+    traffic = None   # dram bytes per launch of the same kernel from the committed ncu --set full capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01c_traffic.json")))["tc_scores_kernel"]
+        if N == 65536 and args.mode == "stochastic":
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except Exception:
+        traffic = None
     roofline = {"kernel": "tc_scores_kernel (tcgen05 split-bf16 UMMA, TMEM accumulators, fused arg-max / Gumbel-max)",
                 "bound": "tensor", "achieved": tc_tflops_issued, "peak": pk["bf16"], "unit": "TFLOP/s",
-                "frac": tc_tflops_issued / pk["bf16"], "traffic": None, "peak_source": pk["source"],
+                "frac": tc_tflops_issued / pk["bf16"], "traffic": traffic, "algorithmic_bytes": alg_bytes,
+                "peak_source": pk["source"],
                 "kernel_ms": tc_ms, "share_of_step": tc_ms / ms_step,
                 "algorithmic_tflops_fp32_equiv": flops / (tc_ms * 1e-3) / 1e12,
                 "hbm": {"achieved_gbs": alg_bytes / (tc_ms * 1e-3) / 1e9, "peak_gbs": pk["hbm"],
