@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 104
+#define B200VQ_VERSION 105
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -233,6 +233,11 @@ int b200vq_gather_owned(const uint64_t* keys, int64_t N, const float* emb_local,
  *   b200vq_weight_grad  dw = x^T y  (x (N,C; ldx), y (N,D)), written as (C,D) or, dw_is_dc == 1,
  *                       (D,C); colsum (C, nullable) = column sums of x (bias grad).  Outputs are
  *                       zeroed inside; accumulation across CTAs uses fp32 atomics.
+ *   b200vq_weight_grad_ws  the same result without atomics: every CTA writes its partial (C*D + C floats)
+ *                       to its own slab of `workspace` (b200vq_weight_grad_workspace_bytes(C, D), 16-byte
+ *                       aligned) and a second kernel adds the slabs in a fixed order (run-to-run
+ *                       deterministic, and faster: no contended atomics).  B200VQ_EINVAL if the
+ *                       workspace is too small.
  *   b200vq_colsum       out (D) = column sums of y (N,D), D <= 32 (in_linear.bias.grad)
  */
 int b200vq_linear_supported(int C, int D);
@@ -242,6 +247,10 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
                       float* y, int64_t ldy, b200vq_stream_t stream);
 int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
                        int dw_is_dc, float* colsum, b200vq_stream_t stream);
+size_t b200vq_weight_grad_workspace_bytes(int C, int D);
+int b200vq_weight_grad_ws(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
+                          int dw_is_dc, float* colsum, void* workspace, size_t workspace_bytes,
+                          b200vq_stream_t stream);
 int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream);
 
 /*

@@ -12,7 +12,8 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-@pytest.mark.parametrize("N,C,D", [(4096, 768, 24), (1000, 768, 16), (129, 512, 8), (1, 64, 32), (300, 1024, 24)])
+@pytest.mark.parametrize("N,C,D", [(4096, 768, 24), (1000, 768, 16), (129, 512, 8), (1, 64, 32), (300, 1024, 24),
+                                   (40000, 768, 24), (19001, 272, 16)])
 def test_linear_in_out_forward_backward(N, C, D):
     torch.manual_seed(N + C + D)
     x = torch.randn(N, C, device=DEV, requires_grad=True)
@@ -36,6 +37,37 @@ def test_linear_in_out_forward_backward(N, C, D):
     for name, a, b in (("grad_x", x.grad, xd.grad), ("grad_w_in", w_in.grad, wid.grad), ("grad_b_in", b_in.grad, bid.grad),
                        ("grad_w_out", w_out.grad, wod.grad), ("grad_b_out", b_out.grad, bod.grad)):
         assert rel_err(a, b) < 1e-3, (name, rel_err(a, b))
+
+
+@pytest.mark.parametrize("N,C,D,dc", [(65536, 768, 24, 0), (30011, 528, 32, 1), (5000, 768, 24, 0), (0, 768, 24, 0)])
+def test_weight_grad_ws_matches_fp64_and_is_deterministic(N, C, D, dc):
+    """b200vq_weight_grad_ws: per-CTA slabs + ordered reduction (no atomics); small N falls back to atomics"""
+    from video_tokenizer_b200 import _lib
+    lib = V.load_library()
+    torch.manual_seed(N + C)
+    x = torch.randn(N, C, device=DEV)
+    y = torch.randn(N, D, device=DEV)
+    ws = torch.empty(int(lib.b200vq_weight_grad_workspace_bytes(C, D)), dtype=torch.uint8, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    outs = []
+    for _ in range(2):
+        ws.fill_(0xFF)                                # NaN patterns: every slab that is read must have been written
+        dw = torch.full((D, C) if dc else (C, D), 7.0, device=DEV)
+        cs = torch.full((C,), 7.0, device=DEV)
+        _lib.check(lib.b200vq_weight_grad_ws(x.data_ptr(), C, y.data_ptr(), N, C, D, dw.data_ptr(), dc, cs.data_ptr(),
+                                             ws.data_ptr(), ws.numel(), st), "wg_ws")
+        outs.append((dw, cs))
+    ref = x.double().t() @ y.double()
+    ref = ref.t() if dc else ref
+    if N == 0:
+        assert outs[0][0].abs().max() == 0 and outs[0][1].abs().max() == 0
+        return
+    assert rel_err(outs[0][0], ref) < 1e-3
+    assert rel_err(outs[0][1], x.double().sum(0)) < 1e-5
+    if N >= 296 * 64:
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert lib.b200vq_weight_grad_ws(x.data_ptr(), C, y.data_ptr(), N, C, D, dw.data_ptr(), dc, cs.data_ptr(),
+                                     ws.data_ptr(), 16, st) != 0       # workspace too small
 
 
 def test_linear_in_strided_rows_and_3d():

@@ -28,6 +28,9 @@ def lin_out_dc():
     i[0] += 1; _lib.check(lib.b200vq_linear_out(a.data_ptr(), N, D, w_in.data_ptr(), 1, None, C, ys[i[0] % 3].data_ptr(), C, st), "out")
 def wgrad():
     i[0] += 1; _lib.check(lib.b200vq_weight_grad(xs[i[0] % 3].data_ptr(), C, a.data_ptr(), N, C, D, dw.data_ptr(), 0, cs.data_ptr(), st), "wg")
+wsb = torch.empty(int(lib.b200vq_weight_grad_workspace_bytes(C, D)), dtype=torch.uint8, device=dev)
+def wgrad_ws():
+    i[0] += 1; _lib.check(lib.b200vq_weight_grad_ws(xs[i[0] % 3].data_ptr(), C, a.data_ptr(), N, C, D, dw.data_ptr(), 0, cs.data_ptr(), wsb.data_ptr(), wsb.numel(), st), "wgws")
 mb = N * C * 4 / 1e6
-for name, fn in (("linear_in(3xTF32)", lin_in), ("linear_out", lin_out), ("linear_out(dc)", lin_out_dc), ("weight_grad", wgrad)):
-    us = t(fn); print(f"{name:20s} {us:7.1f} us  {mb / us / 1e3 * 1e3 / 1e3:.2f} TB/s")
+for name, fn in (("linear_in(3xTF32)", lin_in), ("linear_out", lin_out), ("linear_out(dc)", lin_out_dc), ("weight_grad", wgrad), ("weight_grad_ws", wgrad_ws)):
+    us = t(fn); print(f"{name:20s} {us:7.1f} us  {mb / us:.2f} TB/s")

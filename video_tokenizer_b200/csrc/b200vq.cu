@@ -546,22 +546,29 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     return launch_check();
 }
 
-int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
-                       float* colsum, b200vq_stream_t stream) {
+namespace {
+// partial: nullable workspace of weight_grad_slabs() * (C*D + C) floats -> atomic-free, deterministic
+inline int weight_grad_slabs() { return 2 * sm_count(); }
+int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
+                       float* colsum, float* partial, cudaStream_t st) {
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (!dw) return B200VQ_EINVAL;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = cuda_check(cudaMemsetAsync(dw, 0, static_cast<size_t>(C) * D * sizeof(float), st));
-    if (rc) return rc;
-    if (colsum && (rc = cuda_check(cudaMemsetAsync(colsum, 0, static_cast<size_t>(C) * sizeof(float), st)))) return rc;
+    int rc = B200VQ_OK;
+    const int64_t tiles = (N + kWgTok - 1) / kWgTok;
+    if (tiles < weight_grad_slabs()) partial = nullptr;   // every slab must be written by its CTA
+    if (!partial || N == 0) {
+        if ((rc = cuda_check(cudaMemsetAsync(dw, 0, static_cast<size_t>(C) * D * sizeof(float), st)))) return rc;
+        if (colsum && (rc = cuda_check(cudaMemsetAsync(colsum, 0, static_cast<size_t>(C) * sizeof(float), st)))) return rc;
+    }
     if (N == 0) return B200VQ_OK;
     if (!x || !y || ldx < C) return B200VQ_EINVAL;
     if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15)) return B200VQ_EALIGN;
-    const int64_t tiles = (N + kWgTok - 1) / kWgTok;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>(tiles, 2ll * sm_count()));
+    int wg_dbg = 0;
+    if (const char* env = std::getenv("B200VQ_WG_DEBUG")) wg_dbg = std::atoi(env);
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>(tiles, static_cast<int64_t>(weight_grad_slabs())));
 #define B200VQ_WG(DD)                                                                \
     if ((rc = set_smem(weight_grad_kernel<DD>, wg_smem_bytes<DD>()))) return rc;     \
-    weight_grad_kernel<DD><<<blocks, 256, wg_smem_bytes<DD>(), st>>>(x, ldx, y, N, C, dw, dw_is_dc, colsum)
+    weight_grad_kernel<DD><<<blocks, 256, wg_smem_bytes<DD>(), st>>>(x, ldx, y, N, C, dw, dw_is_dc, colsum, partial, wg_dbg)
     switch (D) {
         case 8: B200VQ_WG(8); break;
         case 16: B200VQ_WG(16); break;
@@ -569,7 +576,29 @@ int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
         default: B200VQ_WG(32); break;
     }
 #undef B200VQ_WG
+    if ((rc = launch_check()) || !partial) return rc;
+    const int total = C * D + C;
+    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
     return launch_check();
+}
+}  // namespace
+
+int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
+                       float* colsum, b200vq_stream_t stream) {
+    return launch_weight_grad(x, ldx, y, N, C, D, dw, dw_is_dc, colsum, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+size_t b200vq_weight_grad_workspace_bytes(int C, int D) {
+    if (C <= 0 || D <= 0) return 0;
+    return static_cast<size_t>(weight_grad_slabs()) * (static_cast<size_t>(C) * D + C) * sizeof(float);
+}
+
+int b200vq_weight_grad_ws(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
+                          float* colsum, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+    if (!workspace || workspace_bytes < b200vq_weight_grad_workspace_bytes(C, D)) return B200VQ_EINVAL;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
+    return launch_weight_grad(x, ldx, y, N, C, D, dw, dw_is_dc, colsum, static_cast<float*>(workspace),
+                              static_cast<cudaStream_t>(stream));
 }
 
 int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream) {
@@ -620,9 +649,9 @@ __global__ void __launch_bounds__(128) input_norms_kernel(const float* __restric
     }
 }
 struct BnLayout {
-    size_t e2, image, vq, ga, gz, gemb, total;
+    size_t e2, image, vq, ga, gz, gemb, wg, total;
 };
-inline BnLayout bn_layout(int64_t N, int D, int64_t K) {
+inline BnLayout bn_layout(int64_t N, int C, int D, int64_t K) {
     BnLayout l;
     size_t off = 0;
     l.e2 = off; off += align_up(static_cast<size_t>(K) * 4);
@@ -631,6 +660,7 @@ inline BnLayout bn_layout(int64_t N, int D, int64_t K) {
     l.ga = off; off += align_up(static_cast<size_t>(N) * D * 4);
     l.gz = off; off += align_up(static_cast<size_t>(N) * D * 4);
     l.gemb = off; off += align_up(static_cast<size_t>(K) * D * 4);
+    l.wg = off; off += align_up(static_cast<size_t>(2 * sm_count()) * (static_cast<size_t>(C) * D + C) * 4);
     l.total = off;
     return l;
 }
@@ -639,9 +669,8 @@ inline BnLayout bn_layout(int64_t N, int D, int64_t K) {
 extern "C" {
 
 size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K) {
-    (void)C;
-    if (N < 0 || K <= 0 || D <= 0) return 0;
-    return bn_layout(N, D, K).total;
+    if (N < 0 || K <= 0 || D <= 0 || C <= 0) return 0;
+    return bn_layout(N, C, D, K).total;
 }
 
 int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
@@ -656,7 +685,7 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
     if (!x || !w_in || !weight || !w_out || !z || !emb || !wnorm || !znorm || !ste || !idx || !zlen || !hist || !hist_first ||
         !losses || !out)
         return B200VQ_EINVAL;
-    const BnLayout l = bn_layout(N, D, K);
+    const BnLayout l = bn_layout(N, C, D, K);
     if (!workspace || workspace_bytes < l.total) return B200VQ_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
     char* ws = static_cast<char*>(workspace);
@@ -693,12 +722,13 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
     if (N <= 0 || K <= 0) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !w_out || !emb || !wnorm || !znorm || !zlen || !idx || !ste) return B200VQ_EINVAL;
-    const BnLayout l = bn_layout(N, D, K);
+    const BnLayout l = bn_layout(N, C, D, K);
     if (!workspace || workspace_bytes < l.total) return B200VQ_EWORKSPACE;
     char* ws = static_cast<char*>(workspace);
     float* ga = reinterpret_cast<float*>(ws + l.ga);      // grad of 'regularized_z'
     float* gz = reinterpret_cast<float*>(ws + l.gz);      // grad of 'projected_z'
     float* gemb = reinterpret_cast<float*>(ws + l.gemb);  // grad of the normalised codebook
+    float* wgp = reinterpret_cast<float*>(ws + l.wg);     // per-CTA weight-gradient slabs
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc;
     const float* ga_in = g_ste;
@@ -707,7 +737,7 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
         if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, false, st))) return rc;
         if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
         ga_in = ga;
-        if (grad_w_out && (rc = b200vq_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, stream))) return rc;
+        if (grad_w_out && (rc = launch_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, wgp, st))) return rc;
     } else {
         if (grad_w_out && (rc = cuda_check(cudaMemsetAsync(grad_w_out, 0, static_cast<size_t>(C) * D * 4, st)))) return rc;
         if (grad_b_out && (rc = cuda_check(cudaMemsetAsync(grad_b_out, 0, static_cast<size_t>(C) * 4, st)))) return rc;
@@ -718,7 +748,7 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
     if (grad_weight && (rc = b200vq_codebook_backward(gemb, g_emb, emb, wnorm, K, D, l2norm, grad_weight, stream))) return rc;
     if (g_z && (rc = add_inplace(gz, g_z, N * D, st))) return rc;
     if (grad_x && (rc = b200vq_linear_out(gz, N, D, w_in, 1, nullptr, C, grad_x, ldgx, stream))) return rc;
-    if (grad_w_in && (rc = b200vq_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, stream))) return rc;
+    if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, st))) return rc;
     if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, stream))) return rc;
     return B200VQ_OK;
 }

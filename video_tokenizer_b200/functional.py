@@ -222,6 +222,11 @@ def _rows2d(x: torch.Tensor) -> Tuple[torch.Tensor, int, int]:
     return t, stride, t.shape[:-1].numel()
 
 
+def _wg_workspace(lib, C, D, device):
+    """slabs of per-CTA partial weight gradients (b200vq_weight_grad_ws: no atomics, deterministic)"""
+    return torch.empty(int(lib.b200vq_weight_grad_workspace_bytes(C, D)), dtype=torch.uint8, device=device)
+
+
 class _LinearIn(torch.autograd.Function):
     """z = x W^T + b with W (D, C): b200vq_linear_in; backward = b200vq_linear_out (grad_x),
     b200vq_weight_grad (grad_W as (D, C)), b200vq_colsum (grad_b)."""
@@ -257,8 +262,9 @@ class _LinearIn(torch.autograd.Function):
             if ctx.needs_input_grad[1]:
                 xx, ldx, _ = _rows2d(x.detach())
                 gw = torch.empty(D, C, dtype=torch.float32, device=gy.device)
-                _lib.check(lib.b200vq_weight_grad(xx.data_ptr(), ldx, gy.data_ptr(), N, C, D, gw.data_ptr(), 1, None, _stream()),
-                           "b200vq_weight_grad(in_linear)")
+                ws = _wg_workspace(lib, C, D, gy.device)
+                _lib.check(lib.b200vq_weight_grad_ws(xx.data_ptr(), ldx, gy.data_ptr(), N, C, D, gw.data_ptr(), 1, None,
+                                                     ws.data_ptr(), ws.numel(), _stream()), "b200vq_weight_grad_ws(in_linear)")
             if ctx.has_bias and ctx.needs_input_grad[2]:
                 gb = torch.empty(D, dtype=torch.float32, device=gy.device)
                 _lib.check(lib.b200vq_colsum(gy.data_ptr(), N, D, gb.data_ptr(), _stream()), "b200vq_colsum")
@@ -301,8 +307,9 @@ class _LinearOut(torch.autograd.Function):
             if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
                 gw = torch.empty(C, D, dtype=torch.float32, device=gy.device)
                 gb = torch.empty(C, dtype=torch.float32, device=gy.device) if ctx.has_bias else None
-                _lib.check(lib.b200vq_weight_grad(g.data_ptr(), ldg, aa.data_ptr(), N, C, D, gw.data_ptr(), 0, _ptr(gb), _stream()),
-                           "b200vq_weight_grad(out_linear)")
+                ws = _wg_workspace(lib, C, D, gy.device)
+                _lib.check(lib.b200vq_weight_grad_ws(g.data_ptr(), ldg, aa.data_ptr(), N, C, D, gw.data_ptr(), 0, _ptr(gb),
+                                                     ws.data_ptr(), ws.numel(), _stream()), "b200vq_weight_grad_ws(out_linear)")
         return ga, gw, gb
 
 
