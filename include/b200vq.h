@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 105
+#define B200VQ_VERSION 106
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -202,6 +202,19 @@ int b200vq_codebook_backward(const float* grad_emb, const float* g_emb, const fl
  */
 int b200vq_decode(const int64_t* idx, int64_t n, const float* weight, int64_t K, int D, int l2norm,
                   float* out, int* bad_flag, b200vq_stream_t stream);
+
+/*
+ * Index -> hidden in one pass (Bottleneck.decode, bottleneck.py:166-168 = get_codebook_entry :327-341 +
+ * out_linear :162-164; LARPTokenizer.decode_from_bottleneck + the decoder's additive latent positional
+ * table, models/larp_tokenizer.py:463-464, 484-487):
+ *   out[i, :] = normalise(weight[idx[i]]) w_out^T + b_out (+ add[i % add_rows, :])
+ * weight (K,D), w_out (C,D), b_out (C, nullable), add (add_rows, C) nullable, out (n, C; row stride ldo,
+ * 16-byte aligned).  The (n, D) code rows never touch HBM.  (C, D) as b200vq_linear_supported.
+ * Out-of-range indices write NaN rows and set *bad_flag (device int, nullable), as b200vq_decode.
+ */
+int b200vq_decode_project(const int64_t* idx, int64_t n, const float* weight, int64_t K, int D, int l2norm,
+                          const float* w_out, const float* b_out, int C, const float* add, int64_t add_rows,
+                          float* out, int64_t ldo, int* bad_flag, b200vq_stream_t stream);
 
 /*
  * Trainer code-usage statistics from the fused histograms

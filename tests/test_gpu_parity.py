@@ -197,6 +197,46 @@ def test_decode_matches_oracle():
         assert got2.shape == (51, 24)
 
 
+@pytest.mark.parametrize("B,n,C,D,K,l2", [(3, 64, 768, 24, 1000, True), (2, 37, 512, 16, 300, False), (1, 1, 64, 8, 7, True),
+                                          (5, 1024, 768, 24, 8192, True)])
+def test_bottleneck_decode_fused_with_positional_table(B, n, C, D, K, l2):
+    """Bottleneck.decode (bottleneck.py:166-168) + the tokenizer's `z + decoder_latent_pe`
+    (larp_tokenizer.py:463-464) in one kernel: b200vq_decode_project against the oracle"""
+    torch.manual_seed(B + n + K)
+    spec = {"name": "bottleneck", "args": {"bottleneck_dim": D, "norm": "none", "regularizer": {"name": "vq", "args": {
+        "codebook_size": K, "l2_normalized": l2, "stochastic": False}}}}
+    m = V.make(spec, args={"token_nums": n, "input_dim": C, "output_dim": C}).to(DEV).eval()
+    with torch.no_grad():
+        m.regularizer.embedding.weight[K // 2] = 0.0          # zero-norm code row: 1e-12 clamp, never NaN
+    idx = torch.randint(0, K, (B, n))
+    idx[0, 0] = K // 2
+    pe = torch.randn(1, n, C)
+    w, wo, bo = (t.detach().cpu() for t in (m.regularizer.embedding.weight, m.out_linear.weight, m.out_linear.bias))
+    ref = O.bottleneck_decode(idx, w.double(), l2, wo.double(), bo.double())
+    with torch.no_grad():
+        got = m.decode(idx.to(DEV))
+        got_pe = m.decode(idx.to(DEV), add=pe.to(DEV))
+    assert got.shape == (B, n, C) and got.dtype == torch.float32
+    assert_close(got.cpu().double(), ref, "decode_project", 1e-3)
+    assert_close(got_pe.cpu().double(), ref + pe.double(), "decode_project+pe", 1e-3)
+    assert torch.isfinite(got).all()
+    # grad-enabled call with trainable weights keeps the piecewise path and the same numbers
+    got2 = m.decode(idx.to(DEV), add=pe.to(DEV))
+    assert_close(got2.detach().cpu().double(), ref + pe.double(), "decode piecewise", 1e-3)
+
+
+def test_decode_project_flags_bad_indices():
+    from video_tokenizer_b200 import _lib
+    lib = V.load_library()
+    w = torch.randn(50, 16, device=DEV); wo = torch.randn(64, 16, device=DEV)
+    idx = torch.tensor([3, 50, -1, 7], device=DEV)
+    out = torch.zeros(4, 64, device=DEV); flag = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _lib.check(lib.b200vq_decode_project(idx.data_ptr(), 4, w.data_ptr(), 50, 16, 1, wo.data_ptr(), None, 64, None, 0,
+                                         out.data_ptr(), 64, flag.data_ptr(), torch.cuda.current_stream().cuda_stream), "dp")
+    assert int(flag) == 1
+    assert torch.isnan(out[1]).all() and torch.isnan(out[2]).all() and torch.isfinite(out[0]).all() and torch.isfinite(out[3]).all()
+
+
 def test_usage_stats_match_reference_golden():
     g = load_golden("code_usage_stats")
     K = int(g["K"])

@@ -277,9 +277,19 @@ class Bottleneck(nn.Module):
     def project_out(self, z_cat):
         return VF.linear_out(z_cat, self.out_linear.weight, self.out_linear.bias)
 
-    def decode(self, bottleneck_rep):
+    def decode(self, bottleneck_rep, add=None):
+        """indices -> hidden (bottleneck.py:166-168).  `add` (optional, (token_nums, C)): folded into the
+        store of the fused kernel -- the tokenizer's `z + decoder_latent_pe` (larp_tokenizer.py:463-464)."""
+        reg = self.regularizer
+        w = self.out_linear.weight
+        if (type(reg) is SimpleVectorQuantizer and bottleneck_rep.is_cuda and not bottleneck_rep.dtype.is_floating_point
+                and w.dtype == torch.float32 and reg.embedding.weight.dtype == torch.float32
+                and VF.linear_dims_supported(w.shape[0], w.shape[1]) and w.shape[1] == reg.dim
+                and not (torch.is_grad_enabled() and (w.requires_grad or reg.embedding.weight.requires_grad))):
+            return VF.decode_project(bottleneck_rep, reg.embedding.weight, reg.l2_normalized, w, self.out_linear.bias, add)
         regularized_z = self.regularizer.decode(bottleneck_rep)
-        return self.project_out(regularized_z)
+        out = self.project_out(regularized_z)
+        return out if add is None else out + add
 
     def _input_norms(self, x):
         with torch.no_grad():

@@ -520,22 +520,25 @@ int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
     return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, true, static_cast<cudaStream_t>(stream));
 }
 
-int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
-                      int64_t ldy, b200vq_stream_t stream) {
+namespace {
+int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
+                      int64_t ldy, const int64_t* gidx, int64_t gK, int gl2, const float* add, int64_t add_rows, int* bad_flag,
+                      cudaStream_t st) {
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
     if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & 15) || (reinterpret_cast<uintptr_t>(w) & 15)) return B200VQ_EALIGN;
+    if (add && (add_rows <= 0 || (reinterpret_cast<uintptr_t>(add) & 15))) return add_rows <= 0 ? B200VQ_EINVAL : B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
     int lo_dbg = 0, lo_grid = 1;   // one 16-warp CTA per SM: the weight staging is paid once per SM
     if (const char* env = std::getenv("B200VQ_LO_DEBUG")) lo_dbg = std::atoi(env);
     if (const char* env = std::getenv("B200VQ_LO_GRID")) lo_grid = std::max(1, std::atoi(env));
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinRows - 1) / kLinRows, static_cast<int64_t>(lo_grid) * sm_count()));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
 #define B200VQ_LIN_OUT(DD)                                                           \
     if ((rc = set_smem(linear_out_kernel<DD>, smem))) return rc;                     \
-    linear_out_kernel<DD><<<blocks, kLinOutThreads, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy, lo_dbg)
+    linear_out_kernel<DD><<<blocks, kLinOutThreads, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy, lo_dbg, gidx, gK, gl2, add, \
+                                                                add_rows, bad_flag)
     switch (D) {
         case 8: B200VQ_LIN_OUT(8); break;
         case 16: B200VQ_LIN_OUT(16); break;
@@ -544,6 +547,22 @@ int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     }
 #undef B200VQ_LIN_OUT
     return launch_check();
+}
+}  // namespace
+
+int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
+                      int64_t ldy, b200vq_stream_t stream) {
+    return launch_linear_out(a, N, D, w, w_is_dc, bias, C, y, ldy, nullptr, 0, 0, nullptr, 0, nullptr,
+                             static_cast<cudaStream_t>(stream));
+}
+
+int b200vq_decode_project(const int64_t* idx, int64_t n, const float* weight, int64_t K, int D, int l2norm, const float* w_out,
+                          const float* b_out, int C, const float* add, int64_t add_rows, float* out, int64_t ldo, int* bad_flag,
+                          b200vq_stream_t stream) {
+    if (n < 0 || K <= 0) return B200VQ_EINVAL;
+    if (n > 0 && !idx) return B200VQ_EINVAL;
+    return launch_linear_out(weight, n, D, w_out, 0, b_out, C, out, ldo, idx, K, l2norm, add, add_rows, bad_flag,
+                             static_cast<cudaStream_t>(stream));
 }
 
 namespace {

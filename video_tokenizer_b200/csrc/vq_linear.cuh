@@ -167,7 +167,12 @@ constexpr int kLinOutThreads = 512;   // 16 warps share one staged weight matrix
 template <int D>
 __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float* __restrict__ a, int64_t N, const float* __restrict__ w,
                                                          int w_is_dc, const float* __restrict__ bias, int C,
-                                                         float* __restrict__ y, int64_t ldy, int dbg) {
+                                                         float* __restrict__ y, int64_t ldy, int dbg,
+                                                         const int64_t* __restrict__ gidx = nullptr, int64_t gK = 0, int gl2 = 0,
+                                                         const float* __restrict__ add = nullptr, int64_t add_rows = 0,
+                                                         int* __restrict__ bad_flag = nullptr) {
+    // Decode variant (gidx != nullptr): row r of the A operand is normalise(a[gidx[r]]) -- `a` is then the
+    // (gK, D) codebook -- and add[(r % add_rows)][:] (a positional table, nullable) joins the bias.
     constexpr int KS = D / 8, DS = D + 4;
     extern __shared__ float s_w[];  // [C][D + 4] tf32 bits, then bias [C]
     float* s_b = s_w + C * DS;
@@ -199,14 +204,45 @@ __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float*
          u += static_cast<int64_t>(gridDim.x) * (kLinOutThreads / 32)) {
         const int64_t r0 = (u >> 2) * 16 + g;
         const int j0 = static_cast<int>(u & 3) * cq, j1 = min(C / 16, j0 + cq);
-        const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
+        int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
         uint32_t fa[KS][4];
+        if (gidx) {
+            ra = __ldg(gidx + ra); rb = __ldg(gidx + rb);
+            const bool bada = ra < 0 || ra >= gK, badb = rb < 0 || rb >= gK;
+            if (bada) ra = 0;
+            if (badb) rb = 0;
+            float va[2 * KS], vb[2 * KS], na = 0.f, nb = 0.f;
 #pragma unroll
-        for (int s = 0; s < KS; ++s) {
-            fa[s][0] = tf32_rna(__ldg(a + ra * D + 8 * s + t));
-            fa[s][1] = tf32_rna(__ldg(a + rb * D + 8 * s + t));
-            fa[s][2] = tf32_rna(__ldg(a + ra * D + 8 * s + t + 4));
-            fa[s][3] = tf32_rna(__ldg(a + rb * D + 8 * s + t + 4));
+            for (int s = 0; s < KS; ++s) {
+                va[2 * s] = __ldg(a + ra * D + 8 * s + t); va[2 * s + 1] = __ldg(a + ra * D + 8 * s + t + 4);
+                vb[2 * s] = __ldg(a + rb * D + 8 * s + t); vb[2 * s + 1] = __ldg(a + rb * D + 8 * s + t + 4);
+                na = fmaf(va[2 * s], va[2 * s], fmaf(va[2 * s + 1], va[2 * s + 1], na));
+                nb = fmaf(vb[2 * s], vb[2 * s], fmaf(vb[2 * s + 1], vb[2 * s + 1], nb));
+            }
+            na += __shfl_xor_sync(0xffffffffu, na, 1); na += __shfl_xor_sync(0xffffffffu, na, 2);
+            nb += __shfl_xor_sync(0xffffffffu, nb, 1); nb += __shfl_xor_sync(0xffffffffu, nb, 2);
+            float sa = gl2 ? 1.f / fmaxf(sqrtf(na), 1e-12f) : 1.f, sb = gl2 ? 1.f / fmaxf(sqrtf(nb), 1e-12f) : 1.f;
+            if (bada) { sa = __int_as_float(0x7fc00000); if (bad_flag && t == 0) *bad_flag = 1; }   // NaN row, as b200vq_decode
+            if (badb) { sb = __int_as_float(0x7fc00000); if (bad_flag && t == 0) *bad_flag = 1; }
+#pragma unroll
+            for (int s = 0; s < KS; ++s) {
+                fa[s][0] = tf32_rna(va[2 * s] * sa); fa[s][1] = tf32_rna(vb[2 * s] * sb);
+                fa[s][2] = tf32_rna(va[2 * s + 1] * sa); fa[s][3] = tf32_rna(vb[2 * s + 1] * sb);
+            }
+        } else {
+#pragma unroll
+            for (int s = 0; s < KS; ++s) {
+                fa[s][0] = tf32_rna(__ldg(a + ra * D + 8 * s + t));
+                fa[s][1] = tf32_rna(__ldg(a + rb * D + 8 * s + t));
+                fa[s][2] = tf32_rna(__ldg(a + ra * D + 8 * s + t + 4));
+                fa[s][3] = tf32_rna(__ldg(a + rb * D + 8 * s + t + 4));
+            }
+        }
+        const float* pa = nullptr;
+        const float* pb = nullptr;
+        if (add) {
+            pa = add + (min(r0, N - 1) % add_rows) * C + 4 * t;
+            pb = add + (min(r0 + 8, N - 1) % add_rows) * C + 4 * t;
         }
         float* ya = y + r0 * ldy + 4 * t;
         float* yb = y + (r0 + 8) * ldy + 4 * t;
@@ -223,6 +259,12 @@ __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float*
                 mma_tf32(acc1, fa[s][0], fa[s][1], fa[s][2], fa[s][3], __float_as_uint(w1[8 * s]), __float_as_uint(w1[8 * s + 4]));
             }
             const float4 bb = *reinterpret_cast<const float4*>(&s_b[16 * j + 4 * t]);
+            if (add) {
+                const float4 ea = __ldg(reinterpret_cast<const float4*>(pa + 16 * j)), eb = __ldg(reinterpret_cast<const float4*>(pb + 16 * j));
+                if (oka) __stcs(reinterpret_cast<float4*>(ya + 16 * j), make_float4(acc0[0] + bb.x + ea.x, acc0[1] + bb.y + ea.y, acc1[0] + bb.z + ea.z, acc1[1] + bb.w + ea.w));
+                if (okb) __stcs(reinterpret_cast<float4*>(yb + 16 * j), make_float4(acc0[2] + bb.x + eb.x, acc0[3] + bb.y + eb.y, acc1[2] + bb.z + eb.z, acc1[3] + bb.w + eb.w));
+                continue;
+            }
             if (oka) __stcs(reinterpret_cast<float4*>(ya + 16 * j), make_float4(acc0[0] + bb.x, acc0[1] + bb.y, acc1[0] + bb.z, acc1[1] + bb.w));
             if (okb) __stcs(reinterpret_cast<float4*>(yb + 16 * j), make_float4(acc0[2] + bb.x, acc0[3] + bb.y, acc1[2] + bb.z, acc1[3] + bb.w));
         }

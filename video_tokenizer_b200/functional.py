@@ -212,6 +212,10 @@ def linears_supported(x: torch.Tensor, weight: torch.Tensor, C: int, D: int) -> 
     return bool(_lib.load().b200vq_linear_supported(C, D))
 
 
+def linear_dims_supported(C: int, D: int) -> bool:
+    return LINEARS == "fused" and not torch.is_autocast_enabled() and bool(_lib.load().b200vq_linear_supported(C, D))
+
+
 def _rows2d(x: torch.Tensor) -> Tuple[torch.Tensor, int, int]:
     """(tensor, row stride, N) for a (..., C) tensor viewed as N rows; copies unless row-uniform
     with a 16-byte aligned base and a stride that is a multiple of 4 elements."""
@@ -342,6 +346,34 @@ def codebook_lookup(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, s
         _lib.check(lib.b200vq_decode(idx.data_ptr(), idx.numel(), w.data_ptr(), K, D, int(l2norm), out.data_ptr(),
                                      None, _stream()), "b200vq_decode")
     return out.reshape(shape) if shape is not None else out.reshape(*indices.shape, D)
+
+
+def decode_project(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, w_out: torch.Tensor, b_out=None,
+                   add=None) -> torch.Tensor:
+    """Bottleneck.decode (bottleneck.py:166-168) in one pass through b200vq_decode_project:
+    (..., n) indices -> (..., n, C) = normalise(weight[idx]) w_out^T + b_out (+ add, an (n, C) table broadcast
+    over the leading dims: the decoder's latent positional embedding, models/larp_tokenizer.py:463-464).
+    Inference only (no autograd graph), like codebook_lookup."""
+    _require_cuda(indices, "indices")
+    _require_cuda(weight, "embedding.weight")
+    lib = _lib.load()
+    idx = indices.reshape(-1).to(torch.int64).contiguous()
+    w = weight.detach().contiguous()
+    wo = w_out.detach().contiguous()
+    K, D = w.shape
+    C = wo.shape[0]
+    add_rows = 0
+    if add is not None:
+        add = add.detach().to(torch.float32).reshape(-1, C).contiguous()
+        add_rows = add.shape[0]
+        if indices.dim() < 1 or indices.shape[-1] != add_rows:
+            raise ValueError(f"add has {add_rows} rows but indices end in {tuple(indices.shape)}")
+    out = torch.empty(*indices.shape, C, dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check(lib.b200vq_decode_project(idx.data_ptr(), idx.numel(), w.data_ptr(), K, D, int(l2norm), wo.data_ptr(),
+                                             _ptr(b_out.detach() if b_out is not None else None), C, _ptr(add), add_rows,
+                                             out.data_ptr(), C, None, _stream()), "b200vq_decode_project")
+    return out
 
 
 def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Tensor:
