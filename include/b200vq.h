@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 106
+#define B200VQ_VERSION 107
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -264,6 +264,18 @@ size_t b200vq_weight_grad_workspace_bytes(int C, int D);
 int b200vq_weight_grad_ws(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
                           int dw_is_dc, float* colsum, void* workspace, size_t workspace_bytes,
                           b200vq_stream_t stream);
+/*
+ * Backward of out_linear in ONE pass over grad_output g (N,C; row stride ldg), instead of
+ * b200vq_linear_in (grad of the input) + b200vq_weight_grad_ws (weight / bias grads) reading it twice:
+ *   ga (N,D) = g w_out (+ ga_add, nullable (N,D));  dw (C,D) = g^T a;  colsum (C, nullable) = column sums of g
+ * a (N,D) = out_linear's input ('regularized_z'), w_out (C,D).  Needs C in {256,512,768,1024} and the
+ * weight matrix + a 96 KiB ring in shared memory (b200vq_grad_out_supported); workspace as
+ * b200vq_weight_grad_workspace_bytes(C, D).  TF32 operands, fp32 accumulate, no atomics.
+ */
+int b200vq_grad_out_supported(int C, int D);
+int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D,
+                    const float* ga_add, float* ga, float* dw, float* colsum, void* workspace,
+                    size_t workspace_bytes, b200vq_stream_t stream);
 int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream);
 
 /*

@@ -70,6 +70,38 @@ def test_weight_grad_ws_matches_fp64_and_is_deterministic(N, C, D, dc):
                                      ws.data_ptr(), 16, st) != 0       # workspace too small
 
 
+@pytest.mark.parametrize("N,C,D,add", [(65536, 768, 24, True), (4099, 512, 16, False), (31, 256, 8, True), (1, 1024, 24, False),
+                                        (10000, 512, 32, True), (33, 768, 24, False)])
+def test_grad_out_single_pass_matches_fp64(N, C, D, add):
+    """b200vq_grad_out: grad of out_linear's input, weight and bias from one pass over grad_output"""
+    from video_tokenizer_b200 import _lib
+    lib = V.load_library()
+    assert lib.b200vq_grad_out_supported(C, D)
+    torch.manual_seed(N + C + D)
+    big = torch.randn(N, C + 8, device=DEV)
+    g = big[:, :C]                                        # row stride C + 8
+    a = torch.randn(N, D, device=DEV)
+    w = torch.randn(C, D, device=DEV) / D ** 0.5
+    extra = torch.randn(N, D, device=DEV) if add else None
+    ga = torch.full((N, D), 9.0, device=DEV); dw = torch.full((C, D), 9.0, device=DEV); db = torch.full((C,), 9.0, device=DEV)
+    ws = torch.empty(int(lib.b200vq_weight_grad_workspace_bytes(C, D)), dtype=torch.uint8, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    outs = []
+    for _ in range(2):
+        ws.fill_(0xFF)
+        _lib.check(lib.b200vq_grad_out(g.data_ptr(), C + 8, a.data_ptr(), w.data_ptr(), N, C, D, extra.data_ptr() if add else None,
+                                       ga.data_ptr(), dw.data_ptr(), db.data_ptr(), ws.data_ptr(), ws.numel(), st), "grad_out")
+        outs.append((ga.clone(), dw.clone(), db.clone()))
+    gd = g.double()
+    ref_ga = gd @ w.double() + (extra.double() if add else 0)
+    assert rel_err(outs[0][0], ref_ga) < 1e-3, rel_err(outs[0][0], ref_ga)
+    assert rel_err(outs[0][1], gd.t() @ a.double()) < 1e-3
+    assert rel_err(outs[0][2], gd.sum(0)) < 1e-5
+    for x, y in zip(outs[0], outs[1]):
+        assert torch.equal(x, y)                          # no atomics: run-to-run identical
+    assert not lib.b200vq_grad_out_supported(272, 16) and not lib.b200vq_grad_out_supported(1280, 24)
+
+
 def test_linear_in_strided_rows_and_3d():
     """x is a batch-strided slice of a larger activation (models/transformer.py:69)."""
     torch.manual_seed(0)

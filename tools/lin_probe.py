@@ -36,6 +36,12 @@ def dec_proj():
     i[0] += 1; _lib.check(lib.b200vq_decode_project(didx.data_ptr(), N, cbk.data_ptr(), 8192, D, 1, w_out.data_ptr(), b_out.data_ptr(), C, pe.data_ptr(), 1024, ys[i[0] % 3].data_ptr(), C, None, st), "dp")
 def dec_torch():
     i[0] += 1; q = torch.nn.functional.normalize(cbk[didx], dim=-1); torch.add(torch.nn.functional.linear(q, w_out, b_out).view(-1, 1024, C), pe, out=ys[i[0] % 3].view(-1, 1024, C))
+ga = torch.empty(N, D, device=dev)
+def grad_out():
+    i[0] += 1; _lib.check(lib.b200vq_grad_out(xs[i[0] % 3].data_ptr(), C, a.data_ptr(), w_out.data_ptr(), N, C, D, None, ga.data_ptr(), dw.data_ptr(), cs.data_ptr(), wsb.data_ptr(), wsb.numel(), st), "go")
+wt = w_out.t().contiguous()
+def lin_in_tf32():
+    i[0] += 1; _lib.check(lib.b200vq_linear_in(xs[i[0] % 3].data_ptr(), C, N, C, wt.data_ptr(), None, D, z.data_ptr(), st), "in")
 mb = N * C * 4 / 1e6
-for name, fn in (("linear_in(3xTF32)", lin_in), ("linear_out", lin_out), ("linear_out(dc)", lin_out_dc), ("weight_grad", wgrad), ("weight_grad_ws", wgrad_ws), ("decode_project+pe", dec_proj), ("decode torch eager", dec_torch)):
+for name, fn in (("linear_in(3xTF32)", lin_in), ("linear_out", lin_out), ("linear_out(dc)", lin_out_dc), ("weight_grad", wgrad), ("weight_grad_ws", wgrad_ws), ("grad_out (fused)", grad_out), ("decode_project+pe", dec_proj), ("decode torch eager", dec_torch)):
     us = t(fn); print(f"{name:20s} {us:7.1f} us  {mb / us:.2f} TB/s")

@@ -2,6 +2,7 @@
 #include "vq_generic.cuh"
 #include "vq_tc_kernel.cuh"
 #include "vq_linear.cuh"
+#include "vq_gradout.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -607,6 +608,72 @@ int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
     return launch_weight_grad(x, ldx, y, N, C, D, dw, dw_is_dc, colsum, nullptr, static_cast<cudaStream_t>(stream));
 }
 
+extern "C++" {
+namespace {
+template <int D>
+int launch_grad_out_d(const float* g, int64_t ldg, const float* a, const float* w, int64_t N, int C, const float* ga_add, float* ga,
+                      float* partial, unsigned blocks, cudaStream_t st) {
+    const size_t smem = go_smem_bytes<D>(C);
+    int rc = B200VQ_OK;
+#define B200VQ_GO(NS)                                                              \
+    if ((rc = set_smem(grad_out_kernel<D, NS>, smem))) return rc;                  \
+    grad_out_kernel<D, NS><<<blocks, kGoThreads, smem, st>>>(g, ldg, a, w, N, ga_add, ga, partial)
+    switch (C / kGoCols) {
+        case 1: B200VQ_GO(1); break;
+        case 2: B200VQ_GO(2); break;
+        case 3: B200VQ_GO(3); break;
+        default: B200VQ_GO(4); break;
+    }
+#undef B200VQ_GO
+    return launch_check();
+}
+size_t grad_out_smem(int C, int D) {
+    switch (D) {
+        case 8: return go_smem_bytes<8>(C);
+        case 16: return go_smem_bytes<16>(C);
+        case 24: return go_smem_bytes<24>(C);
+        default: return go_smem_bytes<32>(C);
+    }
+}
+}  // namespace
+}  // extern "C++"
+
+int b200vq_grad_out_supported(int C, int D) {
+    if (!lin_dim_ok(D) || C < kGoCols || (C % kGoCols) != 0 || C > 4 * kGoCols) return 0;
+    return grad_out_smem(C, D) <= 227 * 1024 ? 1 : 0;
+}
+
+int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D, const float* ga_add,
+                    float* ga, float* dw, float* colsum, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+    if (N < 0) return B200VQ_EINVAL;
+    if (!b200vq_grad_out_supported(C, D)) return B200VQ_EDIM;
+    if (!dw || !ga) return B200VQ_EINVAL;
+    if (!workspace || workspace_bytes < b200vq_weight_grad_workspace_bytes(C, D)) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = B200VQ_OK;
+    if (N == 0) {
+        if ((rc = cuda_check(cudaMemsetAsync(dw, 0, static_cast<size_t>(C) * D * sizeof(float), st)))) return rc;
+        if (colsum && (rc = cuda_check(cudaMemsetAsync(colsum, 0, static_cast<size_t>(C) * sizeof(float), st)))) return rc;
+        return B200VQ_OK;
+    }
+    if (!g || !a || !w_out || ldg < C) return B200VQ_EINVAL;
+    if ((ldg & 3) || (reinterpret_cast<uintptr_t>(g) & 15) || (reinterpret_cast<uintptr_t>(a) & 15) ||
+        (reinterpret_cast<uintptr_t>(workspace) & 15))
+        return B200VQ_EALIGN;
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kGoTok - 1) / kGoTok, static_cast<int64_t>(sm_count())));
+    float* partial = static_cast<float*>(workspace);
+    switch (D) {
+        case 8: rc = launch_grad_out_d<8>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        case 16: rc = launch_grad_out_d<16>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        case 24: rc = launch_grad_out_d<24>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        default: rc = launch_grad_out_d<32>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+    }
+    if (rc) return rc;
+    const int total = C * D + C;
+    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, 0, colsum);
+    return launch_check();
+}
+
 size_t b200vq_weight_grad_workspace_bytes(int C, int D) {
     if (C <= 0 || D <= 0) return 0;
     return static_cast<size_t>(weight_grad_slabs()) * (static_cast<size_t>(C) * D + C) * sizeof(float);
@@ -753,10 +820,18 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
     const float* ga_in = g_ste;
     if (g_out) {
         // grad_a = g_out W_out ; grad_W_out = g_out^T ste ; grad_b_out = column sums of g_out
-        if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, false, st))) return rc;
-        if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
+        static const bool split_env = std::getenv("B200VQ_GRAD_OUT_SPLIT") != nullptr;   // tuning aid: the two-kernel path
+        if (grad_w_out && !split_env && b200vq_grad_out_supported(C, D)) {
+            // one pass over g_out: grad_a (+ g_ste), grad_W_out and grad_b_out together
+            if ((rc = b200vq_grad_out(g_out, ldg, ste, w_out, N, C, D, g_ste, ga, grad_w_out, grad_b_out, wgp,
+                                      b200vq_weight_grad_workspace_bytes(C, D), stream)))
+                return rc;
+        } else {
+            if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, false, st))) return rc;
+            if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
+            if (grad_w_out && (rc = launch_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, wgp, st))) return rc;
+        }
         ga_in = ga;
-        if (grad_w_out && (rc = launch_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, wgp, st))) return rc;
     } else {
         if (grad_w_out && (rc = cuda_check(cudaMemsetAsync(grad_w_out, 0, static_cast<size_t>(C) * D * 4, st)))) return rc;
         if (grad_b_out && (rc = cuda_check(cudaMemsetAsync(grad_b_out, 0, static_cast<size_t>(C) * 4, st)))) return rc;

@@ -1,0 +1,216 @@
+// b200vq -- one pass over grad_output for the backward of out_linear (reference models/bottleneck.py:
+// 162-164 under autograd):
+//     grad_a [n][d]  = sum_c g[n][c] * w[c][d]   (+ ga_add[n][d])        grad of 'regularized_z'
+//     grad_w [c][d]  = sum_n g[n][c] * a[n][d]                            out_linear.weight.grad
+//     grad_b [c]     = sum_n g[n][c]                                      out_linear.bias.grad
+// g (N x C, row stride ldg) is the only large operand (4*C bytes per token); linear_in_kernel +
+// weight_grad_kernel read it twice, this kernel reads it once.  A CTA (16 warps, one per SM,
+// persistent) walks 32-token tiles; a tile is streamed as C/256 stages of 32 tokens x 256 columns
+// through a 3-deep cp.async ring.  In every stage warp w
+//   * owns columns [16w, 16w+16) for grad_w: one m16 tile (rows = columns of g), k = the 32 tokens,
+//     accumulators for all C/256 stages stay in registers for the whole kernel;
+//   * owns tokens [16 (w&1), +16) and columns [32 (w>>1), +32) for grad_a: k = its 32 columns,
+//     accumulated over the tile's stages, then written per column group to shared memory and summed when the tile's rows are stored.
+// The ring is XOR-swizzled (16-byte groups inside each 128-byte segment, keyed by the token's low bits)
+// so that both fragment patterns -- (token = k, column = row) and (token = row, column = k) -- are free
+// of bank conflicts without padding.  grad_w / grad_b leave the CTA as one slab of the workspace;
+// weight_grad_reduce_kernel adds the slabs in a fixed order (no atomics, deterministic).
+#pragma once
+#include "vq_linear.cuh"
+
+namespace b200vq {
+
+constexpr int kGoThreads = 512;
+constexpr int kGoTok = 32;        // tokens per tile
+constexpr int kGoCols = 256;      // columns per stage (16 warps x 16)
+constexpr int kGoRing = 3;        // stages in flight
+
+template <int D>
+__host__ __device__ constexpr size_t go_smem_bytes(int C) {
+    // w [C][YS] | ring [3][32][256] | a tiles [3][32][YS] | grad_a partials [8 column groups][32][D]
+    return (static_cast<size_t>(C) * wg_ystride<D>() + kGoRing * kGoTok * kGoCols + kGoRing * kGoTok * wg_ystride<D>() +
+            8 * kGoTok * D) * 4;
+}
+
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gmem_src, bool valid) {
+    const int bytes = valid ? 16 : 0;     // src-size 0: the 16 bytes are zero-filled, nothing is read
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+                 "l"(gmem_src), "r"(bytes)
+                 : "memory");
+}
+
+// swizzle of a ring row: XOR applied to the column index (floats) of local token row r
+__device__ __forceinline__ int go_swz(int r) { return ((r & 3) << 3) | (r & 4); }
+
+template <int D, int NS>
+__global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __restrict__ g, int64_t ldg, const float* __restrict__ a,
+                                                                 const float* __restrict__ w, int64_t N,
+                                                                 const float* __restrict__ ga_add, float* __restrict__ ga,
+                                                                 float* __restrict__ partial) {
+    constexpr int NT = D / 8, YS = wg_ystride<D>(), C = NS * kGoCols;
+    extern __shared__ float s_go[];
+    float* s_w = s_go;                                   // [C][YS] tf32 bits
+    float* s_ring = s_w + C * YS;                        // [3][32][256] swizzled
+    float* s_a = s_ring + kGoRing * kGoTok * kGoCols;    // [3][32][YS]
+    float* s_ga = s_a + kGoRing * kGoTok * YS;           // [8][32][D]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gq = lane >> 2, t = lane & 3;
+
+    const int64_t tiles = (N + kGoTok - 1) / kGoTok;
+    const int64_t mine = blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;   // tiles of this CTA
+
+    // stage s of this CTA's tile number j goes to ring slot `slot`; the tile's `a` rows ride with stage 0 (slot `aslot`).
+    // All counters are 32-bit and advanced incrementally: 64-bit div / mod by NS or 3 per stage showed up in the SASS.
+    auto issue = [&](int j, int s, int slot, int aslot) {
+        const int64_t tok0 = (static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(j) * gridDim.x) * kGoTok;
+        const int nrows = static_cast<int>(min(static_cast<int64_t>(kGoTok), N - tok0));   // >= 1
+        const float* src = g + tok0 * ldg + s * kGoCols;
+        float* dst = s_ring + slot * (kGoTok * kGoCols);
+#pragma unroll
+        for (int q = 0; q < kGoTok * kGoCols / 4 / kGoThreads; ++q) {
+            const int i = threadIdx.x + q * kGoThreads, r = i >> 6, c4 = i & 63;
+            const bool ok = r < nrows;
+            cp_async16_zfill(dst + r * kGoCols + ((4 * c4) ^ go_swz(r)), src + (ok ? r : 0) * ldg + 4 * c4, ok);
+        }
+        if (s == 0 && threadIdx.x < kGoTok * (D / 4)) {
+            const int r = threadIdx.x / (D / 4), d4 = threadIdx.x - r * (D / 4);
+            const bool ok = r < nrows;
+            cp_async16_zfill(s_a + aslot * (kGoTok * YS) + r * YS + 4 * d4, a + (tok0 + (ok ? r : 0)) * D + 4 * d4, ok);
+        }
+    };
+
+    float acc[NS][NT][4];     // grad_w: (column 256 s + 16 warp + gq [+8], d 8 j + 2 t [+1])
+    float cs[NS][2];          // grad_b partial sums of columns 16 warp + gq, + 8 over this lane's tokens
+    float gacc[NT][4];        // grad_a of the current tile over this warp's 32 columns of every stage
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+        cs[s][0] = cs[s][1] = 0.f;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) acc[s][j][0] = acc[s][j][1] = acc[s][j][2] = acc[s][j][3] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < NT; ++j) gacc[j][0] = gacc[j][1] = gacc[j][2] = gacc[j][3] = 0.f;
+
+    // prologue: two stages in flight, then the weight matrix (overlaps the first loads)
+    const int ntiles = static_cast<int>(mine);
+    // (nj, ns, nslot, naslot): the next stage to issue
+    int nj = 0, ns = 0, nslot = 0, naslot = 0;
+    auto issue_next = [&]() {
+        if (nj < ntiles) issue(nj, ns, nslot, naslot);
+        cp_async_commit();
+        nslot = nslot == kGoRing - 1 ? 0 : nslot + 1;
+        if (++ns == NS) { ns = 0; ++nj; naslot = naslot == kGoRing - 1 ? 0 : naslot + 1; }
+    };
+    issue_next();
+    issue_next();
+    for (int i = threadIdx.x; i < C * D; i += kGoThreads) {
+        const int c = i / D, d = i - c * D;
+        s_w[c * YS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+    }
+
+    auto flush_ga = [&](int j) {   // tile j of this CTA: sum of the 8 column groups' partial rows -> global
+        const int64_t tok0 = (static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(j) * gridDim.x) * kGoTok;
+        const int nel = static_cast<int>(min(static_cast<int64_t>(kGoTok), N - tok0)) * D;
+        for (int i = threadIdx.x; i < nel; i += kGoThreads) {
+            float v = 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v += s_ga[q * (kGoTok * D) + i];
+            const int64_t o = tok0 * D + i;
+            ga[o] = v + (ga_add ? __ldg(ga_add + o) : 0.f);
+        }
+    };
+
+    const int mt = warp & 1, kq = warp >> 1;
+    const int swz_b = go_swz(gq);   // rows 16 mt + gq and + 8 share their low three bits
+    int slot = 0, aslot = 0;
+    for (int j = 0; j < ntiles; ++j) {
+        const float* ta = s_a + aslot * (kGoTok * YS);
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            cp_async_wait<1>();
+            __syncthreads();
+            if (s == 0 && j > 0) flush_ga(j - 1);
+            issue_next();
+            if (s == 0) {
+                // the tile's `a` rows arrived with this stage: round them to tf32 once, in place, instead of in
+                // every warp's fragment loads (all 16 warps read the whole tile in each of the NS stages)
+                float* tw = s_a + aslot * (kGoTok * YS);
+                for (int e = threadIdx.x; e < kGoTok * D; e += kGoThreads) {
+                    const int r = e / D, d = e - r * D;
+                    tw[r * YS + d] = __uint_as_float(tf32_rna(tw[r * YS + d]));
+                }
+                __syncthreads();
+            }
+            const float* tile = s_ring + slot * (kGoTok * kGoCols);
+            slot = slot == kGoRing - 1 ? 0 : slot + 1;
+            // ---- grad_w / grad_b: rows = columns 16 warp + gq (+8), k = tokens
+            const int col = 16 * warp + gq;
+#pragma unroll
+            for (int ks = 0; ks < kGoTok / 8; ++ks) {
+                const float* r0 = tile + (8 * ks + t) * kGoCols;          // token 8 ks + t     : swizzle t << 3
+                const float* r1 = r0 + 4 * kGoCols;                       // token 8 ks + t + 4 : swizzle (t << 3) | 4
+                const float x0 = r0[col ^ (t << 3)], x1 = r0[(col + 8) ^ (t << 3)];
+                const float x2 = r1[col ^ ((t << 3) | 4)], x3 = r1[(col + 8) ^ ((t << 3) | 4)];
+                cs[s][0] += x0 + x2;
+                cs[s][1] += x1 + x3;
+                const uint32_t a0 = tf32_op(x0), a1 = tf32_op(x1), a2 = tf32_op(x2), a3 = tf32_op(x3);
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    const uint32_t b0 = __float_as_uint(ta[(8 * ks + t) * YS + 8 * n + gq]);
+                    const uint32_t b1 = __float_as_uint(ta[(8 * ks + t + 4) * YS + 8 * n + gq]);
+                    mma_tf32(acc[s][n], a0, a1, a2, a3, b0, b1);
+                }
+            }
+            // ---- grad_a: rows = tokens 16 mt + gq (+8), k = columns 32 kq + 8 ks + t (+4) of this stage
+            const float* ra = tile + (16 * mt + gq) * kGoCols;
+            const float* rb = ra + 8 * kGoCols;
+            const float* wb = s_w + (s * kGoCols + 32 * kq) * YS;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const int kc = 32 * kq + 8 * ks + t;   // (kc ^ swz_b) == ((32 kq + t) ^ swz_b) ^ (8 ks): bits 3-4 of 32 kq + t are 0
+                const uint32_t a0 = tf32_op(ra[kc ^ swz_b]), a1 = tf32_op(rb[kc ^ swz_b]);
+                const uint32_t a2 = tf32_op(ra[(kc + 4) ^ swz_b]), a3 = tf32_op(rb[(kc + 4) ^ swz_b]);
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    const uint32_t b0 = __float_as_uint(wb[(8 * ks + t) * YS + 8 * n + gq]);
+                    const uint32_t b1 = __float_as_uint(wb[(8 * ks + t + 4) * YS + 8 * n + gq]);
+                    mma_tf32(gacc[n], a0, a1, a2, a3, b0, b1);
+                }
+            }
+            if (s == NS - 1) {
+                if (NS == 1) __syncthreads();   // the flush of the previous tile (this iteration) reads the same buffer
+                float* buf = s_ga + kq * (kGoTok * D) + (16 * mt + gq) * D + 2 * t;
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    *reinterpret_cast<float2*>(buf + 8 * n) = make_float2(gacc[n][0], gacc[n][1]);
+                    *reinterpret_cast<float2*>(buf + 8 * D + 8 * n) = make_float2(gacc[n][2], gacc[n][3]);
+                    gacc[n][0] = gacc[n][1] = gacc[n][2] = gacc[n][3] = 0.f;
+                }
+            }
+        }
+        aslot = aslot == kGoRing - 1 ? 0 : aslot + 1;
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (ntiles > 0) flush_ga(ntiles - 1);
+
+    // this CTA's slab: [C][D] then [C]
+    float* slab = partial + static_cast<int64_t>(blockIdx.x) * (static_cast<int64_t>(C) * D + C);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+        const int col = s * kGoCols + 16 * warp + gq;
+#pragma unroll
+        for (int n = 0; n < NT; ++n) {
+            *reinterpret_cast<float2*>(slab + col * D + 8 * n + 2 * t) = make_float2(acc[s][n][0], acc[s][n][1]);
+            *reinterpret_cast<float2*>(slab + (col + 8) * D + 8 * n + 2 * t) = make_float2(acc[s][n][2], acc[s][n][3]);
+        }
+        float c0 = cs[s][0], c1 = cs[s][1];
+        c0 += __shfl_xor_sync(0xffffffffu, c0, 1); c0 += __shfl_xor_sync(0xffffffffu, c0, 2);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, 1); c1 += __shfl_xor_sync(0xffffffffu, c1, 2);
+        if (t == 0) {
+            slab[C * D + col] = c0;
+            slab[C * D + col + 8] = c1;
+        }
+    }
+}
+
+}  // namespace b200vq

@@ -19,14 +19,27 @@
 
 namespace b200vq {
 
+// fp32 -> tf32, round to nearest (ties away from zero).  sm_100a has no conversion instruction for this:
+// cvt.rna.tf32.f32 is emulated as FSETP |v| >= inf ; @!p IADD 0x1000 ; LOP3 0xffffe000 (3 issue slots), and the
+// streaming linears convert every operand element.
+//   tf32_rna : the exact tf32 value, low 13 mantissa bits cleared (needed where it is subtracted from v)
+//   tf32_op  : MMA operand only -- the tensor core ignores the low 13 bits, so the mask is dropped
+//              (2 issue slots); NaN / Inf pass through unchanged like cvt.rna
 __device__ __forceinline__ uint32_t tf32_rna(float v) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
     return r;
 }
+__device__ __forceinline__ uint32_t tf32_op(float v) {
+    uint32_t b = __float_as_uint(v);
+    if (fabsf(v) < __int_as_float(0x7f800000)) b += 0x1000u;   // false for NaN
+    return b;
+}
+// 3xTF32 split: v = big + small exactly (fp32 subtraction of a tf32 from its source is exact); the small
+// part goes to the tensor core truncated (that costs ~2^-21 of v, the size of the dropped small*small term)
 __device__ __forceinline__ void tf32_split(float v, uint32_t& big, uint32_t& small) {
     big = tf32_rna(v);
-    small = tf32_rna(v - __uint_as_float(big));
+    small = __float_as_uint(v - __uint_as_float(big));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
                                          uint32_t b1) {
@@ -106,7 +119,7 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
                     tf32_split(a.x, xb[q][0], xs[q][0]); tf32_split(a.y, xb[q][1], xs[q][1]);
                     tf32_split(a.z, xb[q][2], xs[q][2]); tf32_split(a.w, xb[q][3], xs[q][3]);
                 } else {
-                    xb[q][0] = tf32_rna(a.x); xb[q][1] = tf32_rna(a.y); xb[q][2] = tf32_rna(a.z); xb[q][3] = tf32_rna(a.w);
+                    xb[q][0] = tf32_op(a.x); xb[q][1] = tf32_op(a.y); xb[q][2] = tf32_op(a.z); xb[q][3] = tf32_op(a.w);
                 }
             }
 #pragma unroll
@@ -133,7 +146,7 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
                     for (int e = 0; e < 4; ++e) acc[m][j][e] += cm[e] + cc[e];
                 }
                 } else {   // single-pass TF32 (gradients: 1e-3 tolerance), accumulate in the tensor core
-                    const uint32_t wb[4] = {tf32_rna(wv.x), tf32_rna(wv.y), tf32_rna(wv.z), tf32_rna(wv.w)};
+                    const uint32_t wb[4] = {tf32_op(wv.x), tf32_op(wv.y), tf32_op(wv.z), tf32_op(wv.w)};
 #pragma unroll
                     for (int m = 0; m < 2; ++m) {
                         const int qa = 2 * m, qb = 2 * m + 1;
@@ -357,12 +370,12 @@ __global__ void __launch_bounds__(256) weight_grad_kernel(const float* __restric
                     const float2 hi = *reinterpret_cast<const float2*>(bx + (8 * s + t + 4) * kWgStride + 16 * m);
                     cs[m][0] += lo.x + hi.x;
                     cs[m][1] += lo.y + hi.y;
-                    a[m][0] = tf32_rna(lo.x); a[m][1] = tf32_rna(lo.y); a[m][2] = tf32_rna(hi.x); a[m][3] = tf32_rna(hi.y);
+                    a[m][0] = tf32_op(lo.x); a[m][1] = tf32_op(lo.y); a[m][2] = tf32_op(hi.x); a[m][3] = tf32_op(hi.y);
                 }
 #pragma unroll
                 for (int j = 0; j < NT; ++j) {
-                    const uint32_t b0 = tf32_rna(by[(8 * s + t) * YS + 8 * j + g]);
-                    const uint32_t b1 = tf32_rna(by[(8 * s + t + 4) * YS + 8 * j + g]);
+                    const uint32_t b0 = tf32_op(by[(8 * s + t) * YS + 8 * j + g]);
+                    const uint32_t b1 = tf32_op(by[(8 * s + t + 4) * YS + 8 * j + g]);
                     mma_tf32(acc[0][j], a[0][0], a[0][1], a[0][2], a[0][3], b0, b1);
                     mma_tf32(acc[1][j], a[1][0], a[1][1], a[1][2], a[1][3], b0, b1);
                 }

@@ -303,6 +303,16 @@ class _LinearOut(torch.autograd.Function):
         g, ldg, N = _rows2d(gy.to(torch.float32))
         ga = gw = gb = None
         with torch.cuda.device(gy.device):
+            if (ctx.needs_input_grad[0] and ctx.needs_input_grad[1] and lib.b200vq_grad_out_supported(C, D)):
+                # one pass over grad_output: grad_a, grad_W and grad_b together
+                ga = torch.empty(ctx.a_shape, dtype=torch.float32, device=gy.device)
+                gw = torch.empty(C, D, dtype=torch.float32, device=gy.device)
+                gb = torch.empty(C, dtype=torch.float32, device=gy.device) if ctx.has_bias else None
+                ws = _wg_workspace(lib, C, D, gy.device)
+                _lib.check(lib.b200vq_grad_out(g.data_ptr(), ldg, aa.data_ptr(), weight.detach().contiguous().data_ptr(), N, C, D,
+                                               None, ga.data_ptr(), gw.data_ptr(), _ptr(gb), ws.data_ptr(), ws.numel(), _stream()),
+                           "b200vq_grad_out")
+                return ga, gw, gb
             if ctx.needs_input_grad[0]:
                 wt = weight.detach().t().contiguous()   # (D, C)
                 ga = torch.empty(ctx.a_shape, dtype=torch.float32, device=gy.device)
