@@ -566,6 +566,36 @@ int b200vq_decode_project(const int64_t* idx, int64_t n, const float* weight, in
                              static_cast<cudaStream_t>(stream));
 }
 
+extern "C++" {
+namespace {
+template <int D, bool WITH_GA>
+int launch_grad_out_d(const float* g, int64_t ldg, const float* a, const float* w, int64_t N, int C, const float* ga_add, float* ga,
+                      float* partial, unsigned blocks, cudaStream_t st) {
+    const size_t smem = WITH_GA ? go_smem_bytes<D>(C) : go_smem_bytes_wgrad<D>();
+    int rc = B200VQ_OK;
+#define B200VQ_GO(NS)                                                                       \
+    if ((rc = set_smem(grad_out_kernel<D, NS, WITH_GA>, smem))) return rc;                  \
+    grad_out_kernel<D, NS, WITH_GA><<<blocks, kGoThreads, smem, st>>>(g, ldg, a, w, N, ga_add, ga, partial)
+    switch (C / kGoCols) {
+        case 1: B200VQ_GO(1); break;
+        case 2: B200VQ_GO(2); break;
+        case 3: B200VQ_GO(3); break;
+        default: B200VQ_GO(4); break;
+    }
+#undef B200VQ_GO
+    return launch_check();
+}
+size_t grad_out_smem(int C, int D) {
+    switch (D) {
+        case 8: return go_smem_bytes<8>(C);
+        case 16: return go_smem_bytes<16>(C);
+        case 24: return go_smem_bytes<24>(C);
+        default: return go_smem_bytes<32>(C);
+    }
+}
+}  // namespace
+}  // extern "C++"
+
 namespace {
 // partial: nullable workspace of weight_grad_slabs() * (C*D + C) floats -> atomic-free, deterministic
 inline int weight_grad_slabs() { return 2 * sm_count(); }
@@ -574,6 +604,22 @@ int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
     if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
     if (!dw) return B200VQ_EINVAL;
     int rc = B200VQ_OK;
+    static const bool wg_old = std::getenv("B200VQ_WG_OLD") != nullptr;   // tuning aid: the chunk-outer kernel
+    if (partial && N > 0 && !wg_old && (C % kGoCols) == 0 && C <= 4 * kGoCols && x && y && ldx >= C && !(ldx & 3) &&
+        !(reinterpret_cast<uintptr_t>(x) & 15) && !(reinterpret_cast<uintptr_t>(y) & 15)) {
+        // token-outer kernel: every column's accumulators stay in registers, one slab per SM
+        const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kGoTok - 1) / kGoTok, static_cast<int64_t>(sm_count())));
+        switch (D) {
+            case 8: rc = launch_grad_out_d<8, false>(x, ldx, y, nullptr, N, C, nullptr, nullptr, partial, blocks, st); break;
+            case 16: rc = launch_grad_out_d<16, false>(x, ldx, y, nullptr, N, C, nullptr, nullptr, partial, blocks, st); break;
+            case 24: rc = launch_grad_out_d<24, false>(x, ldx, y, nullptr, N, C, nullptr, nullptr, partial, blocks, st); break;
+            default: rc = launch_grad_out_d<32, false>(x, ldx, y, nullptr, N, C, nullptr, nullptr, partial, blocks, st); break;
+        }
+        if (rc) return rc;
+        const int total = C * D + C;
+        weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
+        return launch_check();
+    }
     const int64_t tiles = (N + kWgTok - 1) / kWgTok;
     if (tiles < weight_grad_slabs()) partial = nullptr;   // every slab must be written by its CTA
     if (!partial || N == 0) {
@@ -608,35 +654,6 @@ int b200vq_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
     return launch_weight_grad(x, ldx, y, N, C, D, dw, dw_is_dc, colsum, nullptr, static_cast<cudaStream_t>(stream));
 }
 
-extern "C++" {
-namespace {
-template <int D>
-int launch_grad_out_d(const float* g, int64_t ldg, const float* a, const float* w, int64_t N, int C, const float* ga_add, float* ga,
-                      float* partial, unsigned blocks, cudaStream_t st) {
-    const size_t smem = go_smem_bytes<D>(C);
-    int rc = B200VQ_OK;
-#define B200VQ_GO(NS)                                                              \
-    if ((rc = set_smem(grad_out_kernel<D, NS>, smem))) return rc;                  \
-    grad_out_kernel<D, NS><<<blocks, kGoThreads, smem, st>>>(g, ldg, a, w, N, ga_add, ga, partial)
-    switch (C / kGoCols) {
-        case 1: B200VQ_GO(1); break;
-        case 2: B200VQ_GO(2); break;
-        case 3: B200VQ_GO(3); break;
-        default: B200VQ_GO(4); break;
-    }
-#undef B200VQ_GO
-    return launch_check();
-}
-size_t grad_out_smem(int C, int D) {
-    switch (D) {
-        case 8: return go_smem_bytes<8>(C);
-        case 16: return go_smem_bytes<16>(C);
-        case 24: return go_smem_bytes<24>(C);
-        default: return go_smem_bytes<32>(C);
-    }
-}
-}  // namespace
-}  // extern "C++"
 
 int b200vq_grad_out_supported(int C, int D) {
     if (!lin_dim_ok(D) || C < kGoCols || (C % kGoCols) != 0 || C > 4 * kGoCols) return 0;
@@ -663,10 +680,10 @@ int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kGoTok - 1) / kGoTok, static_cast<int64_t>(sm_count())));
     float* partial = static_cast<float*>(workspace);
     switch (D) {
-        case 8: rc = launch_grad_out_d<8>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        case 16: rc = launch_grad_out_d<16>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        case 24: rc = launch_grad_out_d<24>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        default: rc = launch_grad_out_d<32>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        case 8: rc = launch_grad_out_d<8, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        case 16: rc = launch_grad_out_d<16, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        case 24: rc = launch_grad_out_d<24, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+        default: rc = launch_grad_out_d<32, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
     }
     if (rc) return rc;
     const int total = C * D + C;

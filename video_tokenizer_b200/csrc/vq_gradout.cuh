@@ -26,6 +26,10 @@ constexpr int kGoCols = 256;      // columns per stage (16 warps x 16)
 constexpr int kGoRing = 3;        // stages in flight
 
 template <int D>
+__host__ __device__ constexpr size_t go_smem_bytes_wgrad() {   // WITH_GA = false: ring + a tiles only
+    return (static_cast<size_t>(kGoRing) * kGoTok * kGoCols + kGoRing * kGoTok * wg_ystride<D>()) * 4;
+}
+template <int D>
 __host__ __device__ constexpr size_t go_smem_bytes(int C) {
     // w [C][YS] | ring [3][32][256] | a tiles [3][32][YS] | grad_a partials [8 column groups][32][D]
     return (static_cast<size_t>(C) * wg_ystride<D>() + kGoRing * kGoTok * kGoCols + kGoRing * kGoTok * wg_ystride<D>() +
@@ -42,15 +46,16 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gme
 // swizzle of a ring row: XOR applied to the column index (floats) of local token row r
 __device__ __forceinline__ int go_swz(int r) { return ((r & 3) << 3) | (r & 4); }
 
-template <int D, int NS>
+// WITH_GA = false: weight / bias gradient only (in_linear.weight.grad = gz^T x with g = x, a = gz): no w, no ga.
+template <int D, int NS, bool WITH_GA>
 __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __restrict__ g, int64_t ldg, const float* __restrict__ a,
                                                                  const float* __restrict__ w, int64_t N,
                                                                  const float* __restrict__ ga_add, float* __restrict__ ga,
                                                                  float* __restrict__ partial) {
     constexpr int NT = D / 8, YS = wg_ystride<D>(), C = NS * kGoCols;
     extern __shared__ float s_go[];
-    float* s_w = s_go;                                   // [C][YS] tf32 bits
-    float* s_ring = s_w + C * YS;                        // [3][32][256] swizzled
+    float* s_w = s_go;                                   // [C][YS] tf32 bits (WITH_GA only)
+    float* s_ring = s_w + (WITH_GA ? C * YS : 0);        // [3][32][256] swizzled
     float* s_a = s_ring + kGoRing * kGoTok * kGoCols;    // [3][32][YS]
     float* s_ga = s_a + kGoRing * kGoTok * YS;           // [8][32][D]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gq = lane >> 2, t = lane & 3;
@@ -102,9 +107,11 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
     };
     issue_next();
     issue_next();
-    for (int i = threadIdx.x; i < C * D; i += kGoThreads) {
-        const int c = i / D, d = i - c * D;
-        s_w[c * YS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+    if constexpr (WITH_GA) {
+        for (int i = threadIdx.x; i < C * D; i += kGoThreads) {
+            const int c = i / D, d = i - c * D;
+            s_w[c * YS + d] = __uint_as_float(tf32_rna(__ldg(w + i)));
+        }
     }
 
     auto flush_ga = [&](int j) {   // tile j of this CTA: sum of the 8 column groups' partial rows -> global
@@ -128,7 +135,7 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
         for (int s = 0; s < NS; ++s) {
             cp_async_wait<1>();
             __syncthreads();
-            if (s == 0 && j > 0) flush_ga(j - 1);
+            if (WITH_GA && s == 0 && j > 0) flush_ga(j - 1);
             issue_next();
             if (s == 0) {
                 // the tile's `a` rows arrived with this stage: round them to tf32 once, in place, instead of in
@@ -160,6 +167,7 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
                     mma_tf32(acc[s][n], a0, a1, a2, a3, b0, b1);
                 }
             }
+            if constexpr (!WITH_GA) continue;
             // ---- grad_a: rows = tokens 16 mt + gq (+8), k = columns 32 kq + 8 ks + t (+4) of this stage
             const float* ra = tile + (16 * mt + gq) * kGoCols;
             const float* rb = ra + 8 * kGoCols;
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
     }
     cp_async_wait<0>();
     __syncthreads();
-    if (ntiles > 0) flush_ga(ntiles - 1);
+    if (WITH_GA && ntiles > 0) flush_ga(ntiles - 1);
 
     // this CTA's slab: [C][D] then [C]
     float* slab = partial + static_cast<int64_t>(blockIdx.x) * (static_cast<int64_t>(C) * D + C);
