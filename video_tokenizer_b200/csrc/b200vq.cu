@@ -617,7 +617,7 @@ int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
         }
         if (rc) return rc;
         const int total = C * D + C;
-        weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
+        weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, kWgRedY), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
         return launch_check();
     }
     const int64_t tiles = (N + kWgTok - 1) / kWgTok;
@@ -644,7 +644,7 @@ int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, i
 #undef B200VQ_WG
     if ((rc = launch_check()) || !partial) return rc;
     const int total = C * D + C;
-    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
+    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, kWgRedY), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, dw_is_dc, colsum);
     return launch_check();
 }
 }  // namespace
@@ -687,7 +687,7 @@ int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_
     }
     if (rc) return rc;
     const int total = C * D + C;
-    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, 4), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, 0, colsum);
+    weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, kWgRedY), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, 0, colsum);
     return launch_check();
 }
 
@@ -711,7 +711,7 @@ int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t 
     if (rc || N == 0) return rc;
     if (!y) return B200VQ_EINVAL;
     const int per = 256 / D;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + per - 1) / per, 2ll * sm_count()));
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + per - 1) / per, 8ll * sm_count()));
     colsum_small_kernel<<<blocks, 256, 0, st>>>(y, N, D, out);
     return launch_check();
 }

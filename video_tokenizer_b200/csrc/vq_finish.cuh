@@ -220,13 +220,14 @@ __global__ void __launch_bounds__(1024) usage_stats_kernel(const int32_t* __rest
     nzf = block_sum(nzf); nzb = block_sum(nzb); tot = block_sum(tot);
     double kl = 0, ent = 0;
     if (tot > 0) {
-        const double logK = log(static_cast<double>(K));
+        const float logK = logf(static_cast<float>(K));
         for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
             const int cf = hf[k];
             // avg_probs = one_hot.float().mean(0) -> fp32 count/n ; log(avg + 1e-10) in fp32
             const float avg = static_cast<float>(cf) / static_cast<float>(tot);
             ent -= static_cast<double>(avg * logf(avg + 1e-10f));
-            if (cf > 0) { const double p = cf / tot; kl += p * (log(p) + logK); }
+            // Categorical KL of the reference is fp32 arithmetic (utils/statistics.py:16-19); fp64 log() is ~40x slower here
+            if (cf > 0) kl += static_cast<double>(avg * (logf(avg) + logK));
         }
     }
     kl = block_sum(kl); ent = block_sum(ent);

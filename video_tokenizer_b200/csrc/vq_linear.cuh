@@ -461,21 +461,24 @@ __global__ void __launch_bounds__(256) weight_grad_kernel(const float* __restric
     }
 }
 
-// dw (and colsum) = sum over the CTA slabs written by weight_grad_kernel; block = (64, 4): 4 slab ranges
-__global__ void __launch_bounds__(256) weight_grad_reduce_kernel(const float* __restrict__ partial, int nslabs, int C, int D,
+// dw (and colsum) = sum over the CTA slabs written by weight_grad_kernel / grad_out_kernel; block = (64, 8): 8 slab ranges
+constexpr int kWgRedY = 8;   // slab ranges per block
+__global__ void __launch_bounds__(64 * kWgRedY) weight_grad_reduce_kernel(const float* __restrict__ partial, int nslabs, int C, int D,
                                                                  float* __restrict__ dw, int dw_is_dc, float* __restrict__ colsum) {
-    __shared__ float s_part[4][64];
+    __shared__ float s_part[kWgRedY][64];
     const int total = C * D + C;
     const int i = blockIdx.x * 64 + threadIdx.x;
     float acc = 0.f;
     if (i < total) {
 #pragma unroll 8
-        for (int b = threadIdx.y; b < nslabs; b += 4) acc += partial[static_cast<int64_t>(b) * total + i];
+        for (int b = threadIdx.y; b < nslabs; b += kWgRedY) acc += __ldg(partial + static_cast<int64_t>(b) * total + i);
     }
     s_part[threadIdx.y][threadIdx.x] = acc;
     __syncthreads();
     if (threadIdx.y == 0 && i < total) {
-        const float v = s_part[0][threadIdx.x] + s_part[1][threadIdx.x] + s_part[2][threadIdx.x] + s_part[3][threadIdx.x];
+        float v = 0.f;
+#pragma unroll
+        for (int q = 0; q < kWgRedY; ++q) v += s_part[q][threadIdx.x];
         if (i < C * D) {
             const int c = i / D, d = i - c * D;
             dw[dw_is_dc ? d * C + c : i] = v;
@@ -493,9 +496,18 @@ __global__ void __launch_bounds__(256) colsum_small_kernel(const float* __restri
     __syncthreads();
     const int per = 256 / D, d = threadIdx.x % D, r = threadIdx.x / D;
     float acc = 0.f;
-    if (r < per)
-        for (int64_t n = static_cast<int64_t>(blockIdx.x) * per + r; n < N; n += static_cast<int64_t>(gridDim.x) * per) acc += y[n * D + d];
-    if (r < per) atomicAdd(&s_acc[d], acc);
+    if (r < per) {
+        const int64_t step = static_cast<int64_t>(gridDim.x) * per;
+        int64_t n = static_cast<int64_t>(blockIdx.x) * per + r;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;     // four loads in flight per thread
+        for (; n + 3 * step < N; n += 4 * step) {
+            a0 += __ldg(y + n * D + d); a1 += __ldg(y + (n + step) * D + d);
+            a2 += __ldg(y + (n + 2 * step) * D + d); a3 += __ldg(y + (n + 3 * step) * D + d);
+        }
+        for (; n < N; n += step) a0 += __ldg(y + n * D + d);
+        acc = (a0 + a1) + (a2 + a3);
+        atomicAdd(&s_acc[d], acc);
+    }
     __syncthreads();
     if (threadIdx.x < D) atomicAdd(out + threadIdx.x, s_acc[threadIdx.x]);
 }
