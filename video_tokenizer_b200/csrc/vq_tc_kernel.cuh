@@ -317,8 +317,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         const uint32_t row_local = 32 * (warp & 3) + lane;
         float* q_sc = s_queue + warp * (kQueueSlots * kQueueWords);
         uint2* q_meta = reinterpret_cast<uint2*>(q_sc + kQueueSlots * 8);
-        uint32_t* q_tail = s_qtail + warp;
-        uint32_t qhead = 0;
+        uint32_t qhead = 0, qtail = 0;   // ring positions, warp-uniform
+        const uint32_t lt_mask = (1u << lane) - 1u;
+        const uint32_t flush_min = (p.debug >> 8) & 0xFF ? (p.debug >> 8) & 0xFF : 32u;   // tuning: smallest batch drained at a tile end
         const uint32_t grow0 = static_cast<uint32_t>(p.row_offset + row0);
         const uint32_t k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
         const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
@@ -341,12 +342,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             }
             if (__any_sync(0xffffffffu, evmask != 0u) && !(p.debug & 64)) {
 #pragma unroll
-                for (int hg = 0; hg < 2; ++hg) {   // two groups, then a drain check: the ring never overflows
-#pragma unroll
-                    for (int gg = 0; gg < 2; ++gg) {
-                        const int g = 2 * hg + gg;
-                        if (evmask & (1u << g)) {
-                            const uint32_t slot = atomicAdd(q_tail, 1u) & (kQueueSlots - 1);
+                for (int g = 0; g < 4; ++g) {
+                    // ring slots from a ballot: the tail lives in a (warp-uniform) register, no shared-memory atomic,
+                    // and a group none of the 32 rows cares about costs one VOTE
+                    const uint32_t m = __ballot_sync(0xffffffffu, (evmask >> g) & 1u);
+                    if (m != 0u) {
+                        if ((evmask >> g) & 1u) {
+                            const uint32_t slot = (qtail + __popc(m & lt_mask)) & (kQueueSlots - 1);
                             float* e = q_sc + slot * 8;
                             *reinterpret_cast<uint4*>(e) = make_uint4(v[8 * g], v[8 * g + 1], v[8 * g + 2], v[8 * g + 3]);
                             *reinterpret_cast<uint4*>(e + 4) = make_uint4(v[8 * g + 4], v[8 * g + 5], v[8 * g + 6], v[8 * g + 7]);
@@ -354,19 +356,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                             q_meta[slot] = make_uint2(group0 + 4 * ch + g,
                                                       row_local | (__float2uint_rn(ex2_approx(lh[4 * ch + g])) << 16));
                         }
+                        qtail += __popc(m);
                     }
-                    __syncwarp();
-                    // Drain inside the tile only when the ring could overflow (the next two groups add <= 64):
-                    // while this warp expands groups its half of the accumulator is not released and the
-                    // MMAs of the buffer wait.  The regular drain is at the end of the tile, after the release.
-                    uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead;
-                    if (pending > kQueueSlots - 64u) {
-                        do {
-                            sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
-                            qhead += 32u;
-                            pending -= 32u;
-                        } while (pending >= 32u);
-                        thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);
+                    if (g & 1) {
+                        // Drain inside the tile only when the ring could overflow (the next two groups add <= 64):
+                        // while this warp expands groups its half of the accumulator is not released and the
+                        // MMAs of the buffer wait.  The regular drain is at the end of the tile, after the release.
+                        uint32_t pending = qtail - qhead;
+                        if (pending > kQueueSlots - 64u) {
+                            __syncwarp();
+                            do {
+                                sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
+                                qhead += 32u;
+                                pending -= 32u;
+                            } while (pending >= 32u);
+                            thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);
+                        }
                     }
                 }
             }
@@ -401,13 +406,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
             }
             // regular drain, off the accumulator's critical path
             __syncwarp();
-            for (uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead; pending >= 32u; pending -= 32u) {
-                sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
-                qhead += 32u;
+            for (uint32_t pending = qtail - qhead; pending >= flush_min;) {
+                const uint32_t n = min(32u, pending);
+                sample_flush(q_sc, q_meta, qhead, n, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
+                qhead += n;
+                pending -= n;
             }
         }
         __syncwarp();
-        for (uint32_t pending = *reinterpret_cast<volatile uint32_t*>(q_tail) - qhead; pending != 0u;) {
+        for (uint32_t pending = qtail - qhead; pending != 0u;) {
             const uint32_t n = min(32u, pending);
             sample_flush(q_sc, q_meta, qhead, n, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
             qhead += n;
