@@ -211,10 +211,56 @@ def run_stats():
     print("code_usage_stats:", {k: float(v) for k, v in rec.items() if k not in ("rep", "K")})
 
 
+def _load_ref_fsq():
+    """the UNMODIFIED reference models/model_new/quantizer/fsq.py (needs only torch, einops, numpy)"""
+    import importlib.util
+    import sys
+    from oracle.ref_loader import reference_root
+    path = os.path.join(reference_root(), "models", "model_new", "quantizer", "fsq.py")
+    spec = importlib.util.spec_from_file_location("ref_fsq", path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ref_fsq"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def run_sq(fsq, name, *, shape, D, K, seed, l2, beta=0.25, input_format="blc", frozen=False):
+    """`VectorQuantizer` ('sq' bottleneck): outputs + grads from the reference class itself"""
+    import tempfile
+    torch.manual_seed(seed)
+    W = torch.randn(K, D)
+    if l2:
+        W = torch.nn.functional.normalize(W, dim=-1)      # like the pre-normalised Leech-lattice table
+    W[K // 3] = W[K // 7]                                  # exact tie -> lowest index
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "cb.npy")
+        np.save(path, W.numpy())
+        q = fsq.VectorQuantizer(n_embed=K, embed_dim=D, l2_norm=l2, beta=beta, input_format=input_format,
+                                predefined_codebook=path, freeze_codebook=frozen)
+    q.train()
+    z = torch.randn(*shape, requires_grad=True)
+    out = q(z)
+    G = torch.randn_like(out["output"])
+    ((out["output"] * G).sum() + 0.7 * out["loss_codebook"]).backward()
+    rec = {"z": _np(z), "weight": _np(W), "G": _np(G), "output": _np(out["output"]), "loss_codebook": _np(out["loss_codebook"]),
+           "grad_z": _np(z.grad), "l2": np.array(l2), "beta": np.array(beta), "frozen": np.array(frozen),
+           "input_format": np.array(input_format)}
+    if not frozen:
+        rec["grad_weight"] = _np(q.embedding.weight.grad)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+    print("wrote", name)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
     bott, registry = load_reference()
+    if os.environ.get("GOLDEN_ONLY") == "sq":
+        fsq = _load_ref_fsq()
+        run_sq(fsq, "sq_l2_d24_k1000_blc", shape=(2, 48, 24), D=24, K=1000, seed=21, l2=True)
+        run_sq(fsq, "sq_l2_d24_k4096_frozen", shape=(3, 64, 24), D=24, K=4096, seed=22, l2=True, frozen=True)
+        run_sq(fsq, "sq_nol2_d16_k300_bchw", shape=(2, 16, 5, 6), D=16, K=300, seed=23, l2=False, input_format="bchw")
+        return
     run_vq(bott, "vq_argmin_d16_k500", B=2, n=96, D=16, K=500, seed=1)
     run_vq(bott, "vq_argmin_d24_k1024", B=3, n=64, D=24, K=1024, seed=2)
     run_vq(bott, "vq_argmin_d8_k64", B=1, n=33, D=8, K=64, seed=3)

@@ -233,6 +233,36 @@ def bottleneck_decode(indices, weight, l2_normalized, w_out, b_out):
     return F.linear(codebook_lookup(indices, weight, l2_normalized), w_out, b_out)
 
 
+def sq_forward(z: torch.Tensor, weight: torch.Tensor, l2_norm: bool, beta: float, input_format: str = "blc") -> dict:
+    """`VectorQuantizer.forward` of the sibling quantizer family (models/model_new/quantizer/fsq.py:176-214;
+    built as bottleneck_type 'sq' with K=196 560, D=24, models/larp_tokenizer.py:230-233): nearest code by
+    -cos (l2) or squared distance, loss = beta*mean(sum_d (q.detach()-z)^2) + mean(sum_d (q-z.detach())^2)
+    (:207: summed over the code dimension, then averaged), straight-through output (:209).  Also returns
+    the indices and the usage entropy the reference computes and drops (:195-196, :216-219)."""
+    if input_format == "bchw":
+        z = z.permute(0, 2, 3, 1)
+    D = weight.shape[1]
+    if l2_norm:
+        z = F.normalize(z, dim=-1)
+        z_flat = z.reshape(-1, D)
+        d = -z_flat @ F.normalize(weight, dim=-1).t()
+    else:
+        z_flat = z.reshape(-1, D)
+        d = torch.sum(z_flat ** 2, dim=1, keepdim=True) + torch.sum(weight ** 2, dim=1) - 2 * z_flat @ weight.t()
+    idx = torch.argmin(d.detach(), dim=1)
+    count = torch.bincount(idx, minlength=weight.shape[0]).float()
+    probs = (count + 1e-4) / (count + 1e-4).sum()
+    entropy = -(probs * torch.log(probs)).sum()
+    z_q = F.embedding(idx, weight).view(z.shape)
+    if l2_norm:
+        z_q = F.normalize(z_q, dim=-1)
+    loss = beta * torch.mean(((z_q.detach() - z) ** 2).sum(dim=-1)) + torch.mean(((z_q - z.detach()) ** 2).sum(dim=-1))
+    out = z + (z_q - z).detach()
+    if input_format == "bchw":
+        out = out.permute(0, 3, 1, 2)
+    return {"output": out, "loss_codebook": loss, "indices": idx, "cb_entropy": entropy, "scores": d}
+
+
 def code_usage_stats(rep: torch.Tensor, codebook_size: int) -> dict:
     """Trainer statistics (larp_tokenizer_trainer.py:335-352; utils/statistics.py:5-32).
     ``rep`` (B, n) int64.  index_usage / kl_uni / perplexity use sample 0 only;
