@@ -16,8 +16,9 @@ torch.manual_seed(0)
 spec = {"name": "bottleneck", "args": {"bottleneck_dim": 24, "norm": "none", "regularizer": {"name": "vq", "args": {
     "codebook_size": 8192, "l2_normalized": True, "stochastic": True, "stochastic_temperature": 0.03}}}}
 m = V.make(spec, args={"token_nums": 1024, "input_dim": 768, "output_dim": 768}).to(dev)
-x = torch.randn(8, 1024, 768, device=dev, requires_grad=True)
-G = torch.randn(8, 1024, 768, device=dev)
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+x = torch.randn(B, 1024, 768, device=dev, requires_grad=True)
+G = torch.randn(B, 1024, 768, device=dev)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
 

@@ -58,6 +58,18 @@ class AbstractRegularizer(nn.Module):
         raise NotImplementedError
 
 
+_ZEROS: dict = {}
+
+
+def _zero_scalar(device):
+    """0-dim fp32 zero for the three entropy keys when entropy_loss_weight == 0 (bottleneck.py:303 builds a new
+    tensor per call; a fill kernel + ~10 us of host time per step here).  Shared and read-only by convention."""
+    z = _ZEROS.get(device)
+    if z is None:
+        z = _ZEROS[device] = torch.zeros((), device=device, dtype=torch.float32)
+    return z
+
+
 @register("vq")
 class SimpleVectorQuantizer(AbstractRegularizer):
     """Drop-in for the reference quantizer (bottleneck.py:203-344)."""
@@ -128,7 +140,7 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         """Output dict of forward() (bottleneck.py:312-323) for entropy_loss_weight == 0."""
         self.last_usage = (hist_first, hist)
         self._last_stats = usage
-        zero = torch.zeros((), device=znorm.device, dtype=torch.float32)
+        zero = _zero_scalar(znorm.device)
         out = {
             "unregularized_z": znorm,
             "emb": emb,

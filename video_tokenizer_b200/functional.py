@@ -35,8 +35,31 @@ def _require_cuda(t: torch.Tensor, name: str):
         raise RuntimeError(f"video_tokenizer_b200: '{name}' must be a CUDA tensor (the B200 path has no CPU fallback)")
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
+def _stream(index: Optional[int] = None) -> int:
+    """cudaStream_t of torch's current stream on the current (or given) device.  The raw getter avoids building a
+    torch.cuda.Stream object per call (the host side of a step is ~0.5 ms: every 10 us counts)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device() if index is None else index)
+    return torch.cuda.current_stream(index).cuda_stream
+
+
+class _NullGuard:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NULL_GUARD = _NullGuard()
+
+
+def _on_device(dev: torch.device):
+    """`with torch.cuda.device(dev)` only when dev is not already current (the guard costs ~15 us per use)"""
+    return _NULL_GUARD if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -44,7 +67,7 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    key = (device.index, _stream(device.index))
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
@@ -88,7 +111,7 @@ def prepare_codebook(weight: torch.Tensor, l2norm: bool):
     e2 = torch.empty(K, dtype=torch.float32, device=w.device)
     wnorm = torch.empty(K, dtype=torch.float32, device=w.device)
     lib = _lib.load()
-    with torch.cuda.device(w.device):
+    with _on_device(w.device):
         _lib.check(lib.b200vq_prepare_codebook(w.data_ptr(), K, D, int(l2norm), emb.data_ptr(), e2.data_ptr(),
                                                wnorm.data_ptr(), _stream()), "b200vq_prepare_codebook")
     return emb, e2, wnorm
@@ -103,7 +126,7 @@ def prepare_codebook_tc(emb: torch.Tensor) -> Optional[torch.Tensor]:
     if nbytes == 0:
         return None
     image = torch.empty(nbytes, dtype=torch.uint8, device=emb.device)
-    with torch.cuda.device(emb.device):
+    with _on_device(emb.device):
         _lib.check(lib.b200vq_prepare_codebook_tc(emb.data_ptr(), K, D, image.data_ptr(), _stream()),
                    "b200vq_prepare_codebook_tc")
     return image
@@ -127,7 +150,7 @@ class _VQFunction(torch.autograd.Function):
             raise ValueError(f"latent dim {D} != codebook dim {weight.shape[1]}")
         zz, stride = rows_view(z.detach())
         N = zz.shape[:-1].numel()
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             emb, e2, wnorm = prepare_codebook(weight, l2norm)
             image = None
             if SCORING == "tc" and lib.b200vq_tc_supported(D, int(l2norm), mode):
@@ -165,7 +188,7 @@ class _VQFunction(torch.autograd.Function):
         g_znorm, g_emb, g_ste, g_losses = _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste), _f32c(g_losses)
         need_z, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         grad_z = grad_w = None
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             gz = torch.empty(z_shape, dtype=z_dtype, device=dev)
             grad_emb = torch.empty(K, D, dtype=torch.float32, device=dev)
             rc = lib.b200vq_backward(_ptr(g_ste), _ptr(g_znorm), _ptr(g_losses), znorm.data_ptr(), zlen.data_ptr(),
@@ -242,7 +265,7 @@ class _LinearIn(torch.autograd.Function):
         xx, ldx, N = _rows2d(x.detach())
         w = weight.detach().contiguous()
         y = torch.empty(*x.shape[:-1], D, dtype=torch.float32, device=x.device)
-        with torch.cuda.device(x.device):
+        with _on_device(x.device):
             _lib.check(lib.b200vq_linear_in(xx.data_ptr(), ldx, N, C, w.data_ptr(), _ptr(bias.detach() if bias is not None else None),
                                             D, y.data_ptr(), _stream()), "b200vq_linear_in")
         ctx.save_for_backward(x, weight)
@@ -257,7 +280,7 @@ class _LinearIn(torch.autograd.Function):
         gy = gy.to(torch.float32).contiguous()
         N = gy.numel() // D
         gx = gw = gb = None
-        with torch.cuda.device(gy.device):
+        with _on_device(gy.device):
             w = weight.detach().contiguous()
             if ctx.needs_input_grad[0]:
                 gx = torch.empty(x.shape, dtype=torch.float32, device=gy.device)
@@ -286,7 +309,7 @@ class _LinearOut(torch.autograd.Function):
         aa = a.detach().to(torch.float32).contiguous()
         N = aa.numel() // D
         y = torch.empty(*a.shape[:-1], C, dtype=torch.float32, device=a.device)
-        with torch.cuda.device(a.device):
+        with _on_device(a.device):
             _lib.check(lib.b200vq_linear_out(aa.data_ptr(), N, D, weight.detach().contiguous().data_ptr(), 0,
                                              _ptr(bias.detach() if bias is not None else None), C, y.data_ptr(), C, _stream()),
                        "b200vq_linear_out")
@@ -302,7 +325,7 @@ class _LinearOut(torch.autograd.Function):
         C, D = weight.shape
         g, ldg, N = _rows2d(gy.to(torch.float32))
         ga = gw = gb = None
-        with torch.cuda.device(gy.device):
+        with _on_device(gy.device):
             if (ctx.needs_input_grad[0] and ctx.needs_input_grad[1] and lib.b200vq_grad_out_supported(C, D)):
                 # one pass over grad_output: grad_a, grad_W and grad_b together
                 ga = torch.empty(ctx.a_shape, dtype=torch.float32, device=gy.device)
@@ -352,7 +375,7 @@ def codebook_lookup(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, s
     w = weight.detach().contiguous()
     K, D = w.shape
     out = torch.empty(idx.numel(), D, dtype=torch.float32, device=w.device)
-    with torch.cuda.device(w.device):
+    with _on_device(w.device):
         _lib.check(lib.b200vq_decode(idx.data_ptr(), idx.numel(), w.data_ptr(), K, D, int(l2norm), out.data_ptr(),
                                      None, _stream()), "b200vq_decode")
     return out.reshape(shape) if shape is not None else out.reshape(*indices.shape, D)
@@ -379,7 +402,7 @@ def decode_project(indices: torch.Tensor, weight: torch.Tensor, l2norm: bool, w_
         if indices.dim() < 1 or indices.shape[-1] != add_rows:
             raise ValueError(f"add has {add_rows} rows but indices end in {tuple(indices.shape)}")
     out = torch.empty(*indices.shape, C, dtype=torch.float32, device=w.device)
-    with torch.cuda.device(w.device):
+    with _on_device(w.device):
         _lib.check(lib.b200vq_decode_project(idx.data_ptr(), idx.numel(), w.data_ptr(), K, D, int(l2norm), wo.data_ptr(),
                                              _ptr(b_out.detach() if b_out is not None else None), C, _ptr(add), add_rows,
                                              out.data_ptr(), C, None, _stream()), "b200vq_decode_project")
@@ -392,7 +415,7 @@ def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Ten
     _require_cuda(hist_first, "hist_first")
     lib = _lib.load()
     out = torch.empty(4, dtype=torch.float32, device=hist_first.device)
-    with torch.cuda.device(hist_first.device):
+    with _on_device(hist_first.device):
         _lib.check(lib.b200vq_usage_stats(hist_first.data_ptr(), hist_batch.data_ptr(), hist_first.numel(),
                                           out.data_ptr(), _stream()), "b200vq_usage_stats")
     return out
@@ -424,7 +447,7 @@ class _BottleneckFunction(torch.autograd.Function):
         xx, ldx, N = _rows2d(x.detach())
         lead = x.shape[:-1]
         f32 = dict(dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             out = torch.empty(*lead, C, **f32)
             # one allocation for the (N, D) tensors: projected_z | znorm | ste
             nd = torch.empty(3, *lead, D, **f32)
@@ -458,7 +481,9 @@ class _BottleneckFunction(torch.autograd.Function):
         dev = x.device
 
         def _f32c(t):
-            return None if t is None else t.to(torch.float32).contiguous()
+            if t is None or (t.dtype is torch.float32 and t.is_contiguous()):
+                return t
+            return t.to(torch.float32).contiguous()
 
         g_z, g_znorm, g_emb, g_ste, g_losses = _f32c(g_z), _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste), _f32c(g_losses)
         go, ldg = None, C
@@ -466,7 +491,7 @@ class _BottleneckFunction(torch.autograd.Function):
             go, ldg, _ = _rows2d(g_out.to(torch.float32))
         need = ctx.needs_input_grad
         f32 = dict(dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             xx, ldx, _ = _rows2d(x.detach())
             gx = torch.empty(x.shape, **f32) if need[0] else None
             # every parameter gradient is a view of ONE flat buffer [codebook | W_in | b_in | W_out | b_out]
