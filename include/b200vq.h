@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 107
+#define B200VQ_VERSION 108
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -310,6 +310,10 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
                                const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
                                int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
                                float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
+
+/* out3 = {*a, *b, *c} with 0 for null pointers: packs the upstream gradients of loss_q / loss_commit /
+ * loss_codebook (three separate 0-dim tensors under autograd) into the g_losses vector of the backward calls. */
+int b200vq_pack3(const float* a, const float* b, const float* c, float* out3, b200vq_stream_t stream);
 
 #ifdef __cplusplus
 }

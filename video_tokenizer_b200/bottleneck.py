@@ -154,7 +154,7 @@ class SimpleVectorQuantizer(AbstractRegularizer):
             "codebook_entropy": zero,
         }
         if self.return_usage:
-            st = usage if usage is not None else VF.usage_stats(hist_first, hist)
+            st = (usage if usage is not None else VF.usage_stats(hist_first, hist)).unbind(0)   # one op, four views
             out.update(index_usage=st[0], index_usage_batch=st[1], kl_uni=st[2], perplexity=st[3])
         return out
 
@@ -316,11 +316,11 @@ class Bottleneck(nn.Module):
                 and VF.bottleneck_supported(x, self.in_linear.weight, reg.embedding.weight, self.out_linear.weight)):
             # one host call per direction: in_linear -> quantizer -> out_linear (+ usage statistics)
             mode, t_inv, seed, offset = reg._step_config(x.device)
-            x_hat, projected_z, znorm, emb, ste, idx, losses, hists, usage, norms = VF.bottleneck_step(
+            x_hat, projected_z, znorm, emb, ste, idx, lq, lc, lcb, hists, usage, norms = VF.bottleneck_step(
                 x, self.in_linear.weight, self.in_linear.bias, reg.embedding.weight, self.out_linear.weight,
                 self.out_linear.bias, mode=mode, l2norm=reg.l2_normalized, t_inv=t_inv, beta=reg.beta,
                 w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset)
-            regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, losses, hists[0], hists[1], usage)
+            regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, (lq, lc, lcb), hists[0], hists[1], usage)
             bottleneck_rep = regularized_output.pop("bottleneck_rep")
             input_norm_first, input_norm_last = norms[0], norms[1]
             if self.sync_diagnostics:

@@ -691,6 +691,22 @@ int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_
     return launch_check();
 }
 
+namespace {
+__global__ void pack3_kernel(const float* a, const float* b, const float* c, float* out3) {
+    if (threadIdx.x == 0) {
+        out3[0] = a ? *a : 0.f;
+        out3[1] = b ? *b : 0.f;
+        out3[2] = c ? *c : 0.f;
+    }
+}
+}  // namespace
+
+int b200vq_pack3(const float* a, const float* b, const float* c, float* out3, b200vq_stream_t stream) {
+    if (!out3) return B200VQ_EINVAL;
+    pack3_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a, b, c, out3);
+    return launch_check();
+}
+
 size_t b200vq_weight_grad_workspace_bytes(int C, int D) {
     if (C <= 0 || D <= 0) return 0;
     return static_cast<size_t>(weight_grad_slabs()) * (static_cast<size_t>(C) * D + C) * sizeof(float);

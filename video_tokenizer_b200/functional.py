@@ -421,14 +421,20 @@ def usage_stats(hist_first: torch.Tensor, hist_batch: torch.Tensor) -> torch.Ten
     return out
 
 
-# device index -> (flat gradient buffer, number of gradient floats, (2, K) int32 histograms) of the last
-# one-call backward, for sharded.token_sharded_sync
+# device index -> (flat gradient buffer, number of gradient floats, (2, K) int32 histograms, factor the histogram
+# tail was pre-multiplied by, data pointers of the gradient pieces) of the last one-call backward, for
+# sharded.token_sharded_sync
 LAST_FLAT: dict = {}
 
 
 def _dist_world() -> int:
     import torch.distributed as dist
     return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
+def _dist_backend() -> str:
+    import torch.distributed as dist
+    return str(dist.get_backend()) if (dist.is_available() and dist.is_initialized()) else ""
 
 
 class _BottleneckFunction(torch.autograd.Function):
@@ -471,10 +477,12 @@ class _BottleneckFunction(torch.autograd.Function):
         ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
         ctx.hists = hists
         ctx.mark_non_differentiable(idx, hists, usage, norms)
-        return out, z, znorm, emb, ste, idx, losses, hists, usage, norms
+        # the three losses leave as separate 0-dim outputs: indexing a (3,) output in the caller would put a
+        # SelectBackward node (zeros + copy kernels) per used loss into every backward
+        return out, z, znorm, emb, ste, idx, losses[0], losses[1], losses[2], hists, usage, norms
 
     @staticmethod
-    def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_losses, _gh, _gu, _gn):
+    def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_lq, g_lc, g_lcb, _gh, _gu, _gn):
         x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste = ctx.saved_tensors
         l2norm, beta, w_cb, N, C, D, K, has_b_in, has_b_out = ctx.cfg
         lib = _lib.load()
@@ -485,7 +493,8 @@ class _BottleneckFunction(torch.autograd.Function):
                 return t
             return t.to(torch.float32).contiguous()
 
-        g_z, g_znorm, g_emb, g_ste, g_losses = _f32c(g_z), _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste), _f32c(g_losses)
+        g_z, g_znorm, g_emb, g_ste = _f32c(g_z), _f32c(g_znorm), _f32c(g_emb), _f32c(g_ste)
+        g_lq, g_lc, g_lcb = _f32c(g_lq), _f32c(g_lc), _f32c(g_lcb)
         go, ldg = None, C
         if g_out is not None:
             go, ldg, _ = _rows2d(g_out.to(torch.float32))
@@ -506,15 +515,25 @@ class _BottleneckFunction(torch.autograd.Function):
             hists = ctx.hists if sync else None
             flat = torch.empty(tot + (hists.numel() if sync else 0), **f32)
             if sync:   # usage histograms ride in the same collective (counts are exact in fp32 below 2^24)
-                flat[tot:].copy_(hists.view(-1))
-                LAST_FLAT[dev.index] = (flat, tot, hists)
+                # pre-multiplied by the world size when it is a power of two: one all-reduce(AVG) then yields
+                # averaged gradients AND summed histograms, no separate divide kernel
+                world = _dist_world()
+                scale = world if (world & (world - 1)) == 0 and _dist_backend() == "nccl" else 1
+                torch.mul(hists.view(-1), scale, out=flat[tot:])
             gw = flat[offs[0]:offs[0] + sizes[0]].view(K, D) if need[3] else None
             gw_in = flat[offs[1]:offs[1] + sizes[1]].view(D, C) if need[1] else None
             gb_in = flat[offs[2]:offs[2] + sizes[2]] if (has_b_in and need[2]) else None
             gw_out = flat[offs[3]:offs[3] + sizes[3]].view(C, D) if (need[4] or (has_b_out and need[5])) else None
             gb_out = flat[offs[4]:offs[4] + sizes[4]] if (has_b_out and need[5]) else None
+            if sync:
+                ptrs = frozenset(t.data_ptr() for t in (gw, gw_in, gb_in, gw_out, gb_out) if t is not None)
+                LAST_FLAT[dev.index] = (flat, tot, hists, scale, ptrs)
             if tot != sum(sizes) or any(t is None for t in (gw, gw_in, gb_in, gw_out, gb_out)):
                 flat[:tot].zero_()   # padding / unused pieces must not carry garbage into the all-reduce
+            g_losses = None
+            if g_lq is not None or g_lc is not None or g_lcb is not None:
+                g_losses = torch.empty(3, **f32)
+                _lib.check(lib.b200vq_pack3(_ptr(g_lq), _ptr(g_lc), _ptr(g_lcb), g_losses.data_ptr(), _stream()), "b200vq_pack3")
             ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
             rc = lib.b200vq_bottleneck_backward(
                 _ptr(go), ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,
@@ -538,6 +557,7 @@ def bottleneck_supported(x, w_in, weight, w_out) -> bool:
 
 
 def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset):
-    """-> (output, projected_z, znorm, emb, ste, idx(N,), losses(3), hists(2,K) [batch, first], usage(4), input norms(2))"""
+    """-> (output, projected_z, znorm, emb, ste, idx(N,), loss_q, loss_commit, loss_codebook (0-dim each),
+    hists(2,K) [batch, first], usage(4), input norms(2))"""
     cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset))
     return _BottleneckFunction.apply(x, w_in, b_in, weight, w_out, b_out, cfg)

@@ -80,18 +80,19 @@ def _same_storage(a: torch.Tensor, b: torch.Tensor) -> bool:
 
 
 def _flat_of(grads: Sequence[torch.Tensor]):
-    """(flat, n_grad_floats, hists or None) if every gradient aliases one flat fp32 buffer, else (None, 0, None)."""
+    """(flat, n_grad_floats, hists or None, factor the histogram tail was pre-multiplied by) if every gradient is a
+    piece of one flat fp32 buffer, else (None, 0, None, 1)."""
     g0 = grads[0]
     if g0.is_cuda:
         from . import functional as VF
         packed = VF.LAST_FLAT.get(g0.device.index)
-        if packed is not None and all(_same_storage(g, packed[0]) for g in grads):
-            return packed
+        if packed is not None and all(g.data_ptr() in packed[4] for g in grads):
+            return packed[:4]
     base = g0._base
     if (base is not None and base.dim() == 1 and base.is_contiguous() and base.dtype == torch.float32
             and all(g._base is base for g in grads)):
-        return base, base.numel(), None
-    return None, 0, None
+        return base, base.numel(), None, 1
+    return None, 0, None, 1
 
 
 def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
@@ -106,10 +107,18 @@ def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, t
     # (autograd keeps the storage, so p.grad aliases it): ONE collective over [grads | histograms as fp32]
     if tensors and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         world = dist.get_world_size(group)
-        flat, tot, hists = _flat_of(tensors)
+        flat, tot, hists, scale = _flat_of(tensors)
         if flat is not None:
+            tail_ok = hists is not None and usage is not None and _same_storage(usage[0], hists)
+            if tail_ok and scale == world:
+                # histograms were pre-multiplied by the world size: AVG gives mean gradients and summed counts
+                dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)
+                hists.view(-1).copy_(flat[tot:])
+                return usage
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-            if hists is not None and usage is not None and _same_storage(usage[0], hists):
+            if tail_ok:
+                if scale != 1:
+                    flat[tot:].div_(scale)
                 hists.view(-1).copy_(flat[tot:])
                 flat[:tot].div_(world)
                 return usage
