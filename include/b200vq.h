@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 108
+#define B200VQ_VERSION 109
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -314,6 +314,23 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
 /* out3 = {*a, *b, *c} with 0 for null pointers: packs the upstream gradients of loss_q / loss_commit /
  * loss_codebook (three separate 0-dim tensors under autograd) into the g_losses vector of the backward calls. */
 int b200vq_pack3(const float* a, const float* b, const float* c, float* out3, b200vq_stream_t stream);
+
+/* Streaming entropy regulariser: reference `entropy_loss(-d, temperature=T_e)` (models/bottleneck.py:12-33 as
+ * called at :300-303; the "softmax" loss type, the only one the call site uses) without the N x K affinity,
+ * softmax and log-softmax matrices.  z (N,D): the latents the reference ranks with (l2-normalised when
+ * l2_normalized, i.e. 'unregularized_z'); emb (K,D): 'emb'; both fp32, contiguous, 16-byte aligned; t_inv = 1/T_e.
+ *   forward : out3 = {loss_entropy, per_sample_entropy, codebook_entropy};  saves lse (N), ent (N) =
+ *             sum_k p log p per row, w (K) = d codebook_entropy / d mean-prob; psum (K) and ent_sum (1 double)
+ *             are scratch.
+ *   backward: g3 = device {g_loss_entropy, g_per_sample_entropy, g_codebook_entropy}; c (N) scratch;
+ *             grad_z (N,D) / grad_emb (K,D) written (each nullable = not needed).
+ * b200vq_entropy_supported(D): D in {8,16,24,32}. */
+int b200vq_entropy_supported(int D);
+int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv, float* lse,
+                           float* ent, float* psum, float* w, double* ent_sum, float* out3, b200vq_stream_t stream);
+int b200vq_entropy_backward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv,
+                            const float* lse, const float* ent, const float* w, const float* g3, float* c,
+                            float* grad_z, float* grad_emb, b200vq_stream_t stream);
 
 #ifdef __cplusplus
 }

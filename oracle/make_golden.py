@@ -251,10 +251,40 @@ def run_sq(fsq, name, *, shape, D, K, seed, l2, beta=0.25, input_format="blc", f
     print("wrote", name)
 
 
+def run_entropy(bott, name, *, B, n, D, K, seed, l2, w_ent, T_ent, z_scale=1.0):
+    """`SimpleVectorQuantizer` with entropy_loss_weight > 0 (bottleneck.py:300-304 -> entropy_loss :12-33):
+    outputs, the three entropy scalars and grads from the reference class itself.  The objective puts separate
+    upstream gradients on loss_q, per_sample_entropy and codebook_entropy."""
+    torch.manual_seed(seed)
+    vq = bott.SimpleVectorQuantizer(dim=D, codebook_size=K, l2_normalized=l2, entropy_loss_weight=w_ent,
+                                    entropy_loss_temperature=T_ent)
+    z = torch.randn(B, n, D) * z_scale
+    G = torch.randn(B, n, D)
+    zr = z.clone().requires_grad_(True)
+    out = vq(zr)
+    obj = ((out["regularized_z"] * G).sum() + 0.7 * out["loss_q"] + 0.3 * out["per_sample_entropy"]
+           - 0.2 * out["codebook_entropy"])
+    obj.backward()
+    rec = dict(z=_np(z), weight=_np(vq.embedding.weight), G=_np(G), idx=_np(out["bottleneck_rep"]).astype(np.int64),
+               cfg=np.array([D, K, int(l2)], dtype=np.int64), cfg_f=np.array([w_ent, T_ent], dtype=np.float64),
+               grad_z=_np(zr.grad), grad_weight=_np(vq.embedding.weight.grad))
+    for k in ("loss_q", "loss_commit", "loss_codebook", "loss_entropy", "per_sample_entropy", "codebook_entropy"):
+        rec[k] = _np(out[k])
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+    print(f"{name}: loss_entropy={float(out['loss_entropy']):.6f} sample={float(out['per_sample_entropy']):.6f} "
+          f"avg={float(out['codebook_entropy']):.6f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
     bott, registry = load_reference()
+    if os.environ.get("GOLDEN_ONLY") == "entropy":
+        run_entropy(bott, "ent_l2_d16_k300", B=2, n=70, D=16, K=300, seed=31, l2=True, w_ent=0.1, T_ent=0.01)
+        run_entropy(bott, "ent_l2_d24_k1000_warm", B=3, n=100, D=24, K=1000, seed=32, l2=True, w_ent=0.05, T_ent=0.1)
+        run_entropy(bott, "ent_nol2_d8_k130", B=1, n=129, D=8, K=130, seed=33, l2=False, w_ent=0.2, T_ent=1.0, z_scale=0.3)
+        run_entropy(bott, "ent_l2_d32_k64", B=2, n=33, D=32, K=64, seed=34, l2=True, w_ent=0.1, T_ent=0.02)
+        return
     if os.environ.get("GOLDEN_ONLY") == "sq":
         fsq = _load_ref_fsq()
         run_sq(fsq, "sq_l2_d24_k1000_blc", shape=(2, 48, 24), D=24, K=1000, seed=21, l2=True)

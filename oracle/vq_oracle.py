@@ -71,6 +71,32 @@ def entropy_terms(affinity: torch.Tensor, loss_type: str = "softmax", temperatur
     return sample_entropy - avg_entropy, sample_entropy, avg_entropy
 
 
+def entropy_closed_form(z_flat: torch.Tensor, emb: torch.Tensor, temperature: float, g_loss: float = 1.0,
+                        g_sample: float = 0.0, g_avg: float = 0.0):
+    """The streaming formulation the CUDA passes implement (csrc/vq_entropy.cuh), in float64 with the full matrix:
+    the three scalars of `entropy_loss(-d, temperature)` (bottleneck.py:12-33, "softmax" type) and the closed-form
+    gradients wrt the latent rows and the code rows for upstream gradients (g_loss, g_sample, g_avg) on
+    (loss, sample_entropy, avg_entropy).  Referees autograd of `entropy_terms` in tests/test_entropy.py."""
+    z = z_flat.double()
+    e = emb.double()
+    N = z.shape[0]
+    a = (2 * z @ e.t() - (z ** 2).sum(1, keepdim=True) - (e ** 2).sum(1)) / temperature
+    lse = torch.logsumexp(a, dim=1, keepdim=True)
+    logp = a - lse
+    p = logp.exp()
+    ent = (p * logp).sum(1, keepdim=True)                    # sum_k p log p per row (= -H_i)
+    pbar = p.mean(0)
+    sample = -ent.mean()
+    avg = -(pbar * torch.log(pbar + 1e-5)).sum()
+    w = -(torch.log(pbar + 1e-5) + pbar / (pbar + 1e-5))     # d avg / d pbar_k
+    c = (p * w).sum(1, keepdim=True)
+    cS, cA = g_loss + g_sample, g_avg - g_loss
+    g = p / N * (-cS * (logp - ent) + cA * (w - c))          # d objective / d a_ik
+    gz = (2 / temperature) * (g @ e - z * g.sum(1, keepdim=True))
+    ge = (2 / temperature) * (g.t() @ z - e * g.sum(0).unsqueeze(1))
+    return (sample - avg, sample, avg), gz, ge
+
+
 def vq_scores(z_flat: torch.Tensor, emb: torch.Tensor, stochastic: bool) -> torch.Tensor:
     """The N x K matrix the reference ranks codes by.
 

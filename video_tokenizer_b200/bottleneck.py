@@ -170,11 +170,16 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         self._last_stats = None
         loss_commit, loss_codebook = losses[1], losses[2]
         if self.entropy_loss_weight > 0:
-            # N x K by definition (reference :300-303); torch on the device, weight is 0 in all cfgs
-            zf = znorm.reshape(-1, self.dim)
-            d = (torch.sum(zf ** 2, dim=1, keepdim=True) + torch.sum(emb ** 2, dim=1)
-                 - 2 * torch.einsum("bd,dn->bn", zf, emb.t()))
-            loss_entropy, sample_entropy, avg_entropy = entropy_loss(-d, temperature=self.entropy_loss_temperature)
+            if VF.entropy_supported(self.dim):
+                # streamed: the N x K affinity / softmax matrices of reference :300-303 never exist
+                loss_entropy, sample_entropy, avg_entropy = VF.entropy_loss_streamed(
+                    znorm, emb, self.entropy_loss_temperature)
+            else:
+                # code dims without a streaming specialisation: the reference's N x K formulation in torch
+                zf = znorm.reshape(-1, self.dim)
+                d = (torch.sum(zf ** 2, dim=1, keepdim=True) + torch.sum(emb ** 2, dim=1)
+                     - 2 * torch.einsum("bd,dn->bn", zf, emb.t()))
+                loss_entropy, sample_entropy, avg_entropy = entropy_loss(-d, temperature=self.entropy_loss_temperature)
             loss = self.beta * loss_commit + self.codebook_loss_weight * loss_codebook \
                 + self.entropy_loss_weight * loss_entropy
         else:

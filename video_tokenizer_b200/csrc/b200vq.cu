@@ -3,6 +3,7 @@
 #include "vq_tc_kernel.cuh"
 #include "vq_linear.cuh"
 #include "vq_gradout.cuh"
+#include "vq_entropy.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -877,6 +878,103 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
     if (grad_x && (rc = b200vq_linear_out(gz, N, D, w_in, 1, nullptr, C, grad_x, ldgx, stream))) return rc;
     if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, st))) return rc;
     if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, stream))) return rc;
+    return B200VQ_OK;
+}
+
+}  // extern "C"
+
+// ---- streaming entropy regulariser (vq_entropy.cuh) --------------------------------------------------
+namespace {
+template <int PASS>
+int launch_entropy(int D, const EntropyArgs& a, dim3 grid, cudaStream_t st) {
+    switch (D) {
+        case 8: entropy_pass_kernel<8, PASS><<<grid, kEntThreads, 0, st>>>(a); break;
+        case 16: entropy_pass_kernel<16, PASS><<<grid, kEntThreads, 0, st>>>(a); break;
+        case 24: entropy_pass_kernel<24, PASS><<<grid, kEntThreads, 0, st>>>(a); break;
+        case 32: entropy_pass_kernel<32, PASS><<<grid, kEntThreads, 0, st>>>(a); break;
+        default: return B200VQ_EDIM;
+    }
+    return launch_check();
+}
+inline int64_t round_tile(int64_t v) { return (v + kEntTile - 1) / kEntTile * kEntTile; }
+// code-owned passes: split the streamed rows so that the grid covers the machine
+inline void code_owned_grid(int64_t K, int64_t N, dim3* grid, int64_t* per) {
+    const int64_t gx = (K + kEntThreads - 1) / kEntThreads;
+    int64_t splits = std::max<int64_t>(1, (4ll * sm_count() + gx - 1) / gx);
+    splits = std::min<int64_t>(std::min<int64_t>(splits, (N + kEntTile - 1) / kEntTile), 65535);
+    *per = round_tile((N + splits - 1) / splits);
+    splits = (N + *per - 1) / *per;
+    *grid = dim3(static_cast<unsigned>(gx), static_cast<unsigned>(splits));
+}
+}  // namespace
+
+extern "C" {
+
+int b200vq_entropy_supported(int D) { return (D == 8 || D == 16 || D == 24 || D == 32) ? 1 : 0; }
+
+int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv, float* lse,
+                           float* ent, float* psum, float* w, double* ent_sum, float* out3, b200vq_stream_t stream) {
+    if (!b200vq_entropy_supported(D)) return B200VQ_EDIM;
+    if (N <= 0 || K <= 0 || !z || !emb || !lse || !ent || !psum || !w || !ent_sum || !out3 || !(t_inv > 0.f))
+        return B200VQ_EINVAL;
+    if ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(emb)) & 15) return B200VQ_EALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc;
+    if ((rc = cuda_check(cudaMemsetAsync(psum, 0, static_cast<size_t>(K) * sizeof(float), st)))) return rc;
+    if ((rc = cuda_check(cudaMemsetAsync(ent_sum, 0, sizeof(double), st)))) return rc;
+    const float inv_n = 1.0f / static_cast<float>(N);
+    EntropyArgs a{};
+    a.t_inv = t_inv;
+    a.inv_n = inv_n;
+    // rows own, codes stream: lse_i, ent_i, sum of ent
+    a.own = z; a.n_own = N; a.str = emb; a.n_str = K; a.str_per_split = round_tile(K);
+    a.out_a = lse; a.out_b = ent; a.out_sum = ent_sum;
+    if ((rc = launch_entropy<ENT_ROWSTATS>(D, a, dim3(static_cast<unsigned>((N + kEntThreads - 1) / kEntThreads)), st)))
+        return rc;
+    // codes own, rows stream: psum_k
+    EntropyArgs b{};
+    b.t_inv = t_inv;
+    b.inv_n = inv_n;
+    b.own = emb; b.n_own = K; b.str = z; b.n_str = N; b.str_a = lse; b.out_a = psum;
+    dim3 grid;
+    code_owned_grid(K, N, &grid, &b.str_per_split);
+    if ((rc = launch_entropy<ENT_COLSUM>(D, b, grid, st))) return rc;
+    entropy_finalize_kernel<<<1, 1024, 0, st>>>(psum, K, inv_n, ent_sum, w, out3);
+    return launch_check();
+}
+
+int b200vq_entropy_backward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv,
+                            const float* lse, const float* ent, const float* w, const float* g3, float* c,
+                            float* grad_z, float* grad_emb, b200vq_stream_t stream) {
+    if (!b200vq_entropy_supported(D)) return B200VQ_EDIM;
+    if (N <= 0 || K <= 0 || !z || !emb || !lse || !ent || !w || !g3 || !c || !(t_inv > 0.f)) return B200VQ_EINVAL;
+    if ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(emb) | reinterpret_cast<uintptr_t>(grad_z)) & 15)
+        return B200VQ_EALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc;
+    const float inv_n = 1.0f / static_cast<float>(N);
+    const dim3 row_grid(static_cast<unsigned>((N + kEntThreads - 1) / kEntThreads));
+    EntropyArgs a{};
+    a.t_inv = t_inv;
+    a.inv_n = inv_n;
+    a.own = z; a.n_own = N; a.str = emb; a.n_str = K; a.str_per_split = round_tile(K);
+    a.own_a = lse; a.str_a = w; a.out_a = c;
+    if ((rc = launch_entropy<ENT_ROWDOT>(D, a, row_grid, st))) return rc;
+    if (grad_z) {
+        a.own_b = ent; a.own_c = c; a.g3 = g3; a.out_a = nullptr; a.out_vec = grad_z;
+        if ((rc = launch_entropy<ENT_GRAD_ROWS>(D, a, row_grid, st))) return rc;
+    }
+    if (grad_emb) {
+        if ((rc = cuda_check(cudaMemsetAsync(grad_emb, 0, static_cast<size_t>(K) * D * sizeof(float), st)))) return rc;
+        EntropyArgs b{};
+        b.t_inv = t_inv;
+        b.inv_n = inv_n;
+        b.own = emb; b.n_own = K; b.str = z; b.n_str = N;
+        b.own_a = w; b.str_a = lse; b.str_b = ent; b.str_c = c; b.g3 = g3; b.out_vec = grad_emb;
+        dim3 grid;
+        code_owned_grid(K, N, &grid, &b.str_per_split);
+        if ((rc = launch_entropy<ENT_GRAD_CODES>(D, b, grid, st))) return rc;
+    }
     return B200VQ_OK;
 }
 

@@ -214,6 +214,77 @@ def vq_quantize(z, weight, *, mode, l2norm, t_inv=1.0, beta=0.25, w_cb=1.0, n_fi
                              int(n_first), int(seed), int(offset))
 
 
+class _EntropyFunction(torch.autograd.Function):
+    """Streaming `entropy_loss(-d, temperature=T_e)` (reference models/bottleneck.py:12-33 as called at
+    :300-303): b200vq_entropy_forward / _backward.  Inputs are the tensors the reference builds d from
+    ('unregularized_z' rows and 'emb'); the N x K affinity / softmax / log-softmax matrices never exist."""
+
+    @staticmethod
+    def forward(ctx, znorm, emb, t_inv):
+        _require_cuda(znorm, "z")
+        _require_cuda(emb, "emb")
+        lib = _lib.load()
+        dev = znorm.device
+        D = znorm.shape[-1]
+        K = emb.shape[0]
+        zz = znorm.detach().reshape(-1, D).to(torch.float32).contiguous()
+        ee = emb.detach().to(torch.float32).contiguous()
+        N = zz.shape[0]
+        f32 = dict(dtype=torch.float32, device=dev)
+        with _on_device(dev):
+            lse = torch.empty(N, **f32)
+            ent = torch.empty(N, **f32)
+            psum = torch.empty(K, **f32)
+            w = torch.empty(K, **f32)
+            ent_sum = torch.empty(1, dtype=torch.float64, device=dev)
+            out3 = torch.empty(3, **f32)
+            rc = lib.b200vq_entropy_forward(zz.data_ptr(), N, D, ee.data_ptr(), K, float(t_inv), lse.data_ptr(),
+                                            ent.data_ptr(), psum.data_ptr(), w.data_ptr(), ent_sum.data_ptr(),
+                                            out3.data_ptr(), _stream())
+            _lib.check(rc, "b200vq_entropy_forward")
+        ctx.save_for_backward(zz, ee, lse, ent, w)
+        ctx.cfg = (float(t_inv), N, D, K, tuple(znorm.shape), tuple(emb.shape))
+        l, s, a = out3.unbind(0)
+        return l, s, a
+
+    @staticmethod
+    def backward(ctx, g_loss, g_sample, g_avg):
+        zz, ee, lse, ent, w = ctx.saved_tensors
+        t_inv, N, D, K, z_shape, e_shape = ctx.cfg
+        lib = _lib.load()
+        dev = zz.device
+        f32 = dict(dtype=torch.float32, device=dev)
+
+        def _s(t):
+            return None if t is None else t.to(torch.float32).contiguous()
+
+        g_loss, g_sample, g_avg = _s(g_loss), _s(g_sample), _s(g_avg)
+        need_z, need_e = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gz = ge = None
+        with _on_device(dev):
+            g3 = torch.empty(3, **f32)
+            _lib.check(lib.b200vq_pack3(_ptr(g_loss), _ptr(g_sample), _ptr(g_avg), g3.data_ptr(), _stream()), "b200vq_pack3")
+            c = torch.empty(N, **f32)
+            if need_z:
+                gz = torch.empty(N, D, **f32)
+            if need_e:
+                ge = torch.empty(K, D, **f32)
+            rc = lib.b200vq_entropy_backward(zz.data_ptr(), N, D, ee.data_ptr(), K, t_inv, lse.data_ptr(), ent.data_ptr(),
+                                             w.data_ptr(), g3.data_ptr(), c.data_ptr(), _ptr(gz), _ptr(ge), _stream())
+            _lib.check(rc, "b200vq_entropy_backward")
+        return (gz.reshape(z_shape) if gz is not None else None), (ge.reshape(e_shape) if ge is not None else None), None
+
+
+def entropy_supported(D: int) -> bool:
+    return bool(_lib.load().b200vq_entropy_supported(int(D)))
+
+
+def entropy_loss_streamed(znorm, emb, temperature=0.01):
+    """(loss_entropy, per_sample_entropy, codebook_entropy) of reference `entropy_loss(-d, temperature)`
+    (models/bottleneck.py:12-33, :300-303) with d the squared distances between `znorm` rows and `emb` rows."""
+    return _EntropyFunction.apply(znorm, emb, 1.0 / float(temperature))
+
+
 # "fused": the Bottleneck's in/out linears run through the streaming kernels of libb200vq.so when
 # the shapes allow (fp32, D in {8,16,24,32}, C % 16 == 0, no autocast); "torch": always F.linear.
 LINEARS = os.environ.get("B200VQ_LINEARS", "fused")
