@@ -275,6 +275,53 @@ def run_entropy(bott, name, *, B, n, D, K, seed, l2, w_ent, T_ent, z_scale=1.0):
           f"avg={float(out['codebook_entropy']):.6f}")
 
 
+def _load_ref_cosmos():
+    """the UNMODIFIED reference models/cosmos.py under a stub `models` package that only provides `register`"""
+    import importlib.util
+    import sys
+    import types
+    from oracle.ref_loader import reference_root
+    saved = sys.modules.get("models")
+    shell = types.ModuleType("models")
+    shell.__path__ = []
+    shell.register = lambda name: (lambda cls: cls)
+    sys.modules["models"] = shell
+    try:
+        spec = importlib.util.spec_from_file_location("ref_cosmos", os.path.join(reference_root(), "models", "cosmos.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["ref_cosmos"] = mod
+        spec.loader.exec_module(mod)
+    finally:
+        if saved is None:
+            sys.modules.pop("models", None)
+        else:
+            sys.modules["models"] = saved
+    return mod
+
+
+def run_simvq(cosmos, name, *, shape, K, seed, beta=0.25, legacy=True):
+    """`SimVQ` (models/cosmos.py:772-876): outputs + grads from the reference class itself"""
+    torch.manual_seed(seed)
+    D = shape[1]
+    q = cosmos.SimVQ(n_e=K, e_dim=D, beta=beta, legacy=legacy)
+    with torch.no_grad():
+        q.embedding.weight[K // 3] = q.embedding.weight[K // 7]     # exact tie -> lowest index
+    z = (torch.randn(*shape) * 0.5).requires_grad_(True)
+    z_q, loss, (_, ind) = q(z)
+    G = torch.randn_like(z_q)
+    ((z_q * G).sum() + 0.7 * loss).backward()
+    assert q.embedding.weight.grad is None
+    rec = {"z": _np(z), "anchors": _np(q.embedding.weight), "proj_w": _np(q.embedding_proj.weight),
+           "proj_b": _np(q.embedding_proj.bias), "G": _np(G), "z_q": _np(z_q), "loss": _np(loss),
+           "indices": _np(ind).astype(np.int64), "grad_z": _np(z.grad), "grad_proj_w": _np(q.embedding_proj.weight.grad),
+           "grad_proj_b": _np(q.embedding_proj.bias.grad), "beta": np.array(beta), "legacy": np.array(legacy)}
+    idx2 = ind[:1]
+    rec["entry_indices"] = _np(idx2).astype(np.int64)
+    rec["entry"] = _np(q.get_codebook_entry(idx2))
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+    print("wrote", name, "loss", float(loss))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
@@ -284,6 +331,13 @@ def main():
         run_entropy(bott, "ent_l2_d24_k1000_warm", B=3, n=100, D=24, K=1000, seed=32, l2=True, w_ent=0.05, T_ent=0.1)
         run_entropy(bott, "ent_nol2_d8_k130", B=1, n=129, D=8, K=130, seed=33, l2=False, w_ent=0.2, T_ent=1.0, z_scale=0.3)
         run_entropy(bott, "ent_l2_d32_k64", B=2, n=33, D=32, K=64, seed=34, l2=True, w_ent=0.1, T_ent=0.02)
+        return
+    if os.environ.get("GOLDEN_ONLY") == "simvq":
+        cosmos = _load_ref_cosmos()
+        run_simvq(cosmos, "simvq_image_d16_k300", shape=(2, 16, 5, 6), K=300, seed=41)
+        run_simvq(cosmos, "simvq_video_d24_k1000_nonlegacy", shape=(2, 24, 3, 4, 5), K=1000, seed=42, legacy=False)
+        run_simvq(cosmos, "simvq_video_d320_k200", shape=(1, 320, 2, 3, 3), K=200, seed=43)
+        run_simvq(cosmos, "simvq_image_d40_k129", shape=(3, 40, 4, 4), K=129, seed=44, beta=0.5)
         return
     if os.environ.get("GOLDEN_ONLY") == "sq":
         fsq = _load_ref_fsq()

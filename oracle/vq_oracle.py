@@ -289,6 +289,32 @@ def sq_forward(z: torch.Tensor, weight: torch.Tensor, l2_norm: bool, beta: float
     return {"output": out, "loss_codebook": loss, "indices": idx, "cb_entropy": entropy, "scores": d}
 
 
+def simvq_forward(z: torch.Tensor, anchors: torch.Tensor, proj_w: torch.Tensor, proj_b: torch.Tensor, beta: float,
+                  legacy: bool = True) -> dict:
+    """`SimVQ.forward` (models/cosmos.py:792-855): frozen anchor table through one Linear (:810), nearest projected
+    code by squared distance (:814-819), legacy / non-legacy loss weighting (:826-831), straight-through output
+    (:835), channel-first in and out (:795-803, :838-847).  z: (B,C,H,W) or (B,C,T,H,W)."""
+    video = z.dim() == 5
+    z_cl = (z.permute(0, 2, 3, 4, 1) if video else z.permute(0, 2, 3, 1)).contiguous()
+    D = anchors.shape[1]
+    z_flat = z_cl.view(-1, D)
+    table = F.linear(anchors, proj_w, proj_b)
+    d = torch.sum(z_flat ** 2, dim=1, keepdim=True) + torch.sum(table ** 2, dim=1) - 2 * z_flat @ table.t()
+    idx = torch.argmin(d, dim=1)
+    z_q = F.embedding(idx, table).view(z_cl.shape)
+    commit = torch.mean((z_q.detach() - z_cl) ** 2)
+    codebook = torch.mean((z_q - z_cl.detach()) ** 2)
+    loss = commit + beta * codebook if legacy else beta * commit + codebook
+    z_q = z_cl + (z_q - z_cl).detach()
+    if video:
+        z_q = z_q.permute(0, 4, 1, 2, 3).contiguous()
+        ind = idx.view(z.shape[0], z.shape[2], z.shape[3], z.shape[4])
+    else:
+        z_q = z_q.permute(0, 3, 1, 2).contiguous()
+        ind = idx.view(z.shape[0], z.shape[2], z.shape[3])
+    return {"z_q": z_q, "loss": loss, "indices": ind, "scores": d.detach(), "table": table}
+
+
 def code_usage_stats(rep: torch.Tensor, codebook_size: int) -> dict:
     """Trainer statistics (larp_tokenizer_trainer.py:335-352; utils/statistics.py:5-32).
     ``rep`` (B, n) int64.  index_usage / kl_uni / perplexity use sample 0 only;

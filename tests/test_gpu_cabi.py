@@ -76,7 +76,7 @@ def test_invalid_arguments_return_codes():
     t = torch.zeros(64, device=DEV)
     assert lib.b200vq_scores_partial(t.data_ptr(), 7, 16, 4, 16, t.data_ptr(), t.data_ptr(), 4, 0, 0, 1, 1.0, 0, 0, 0,
                                      t.data_ptr(), _stream()) == -1
-    assert lib.b200vq_scores_partial(t.data_ptr(), 0, 300, 4, 300, t.data_ptr(), t.data_ptr(), 4, 0, 0, 1, 1.0, 0, 0, 0,
+    assert lib.b200vq_scores_partial(t.data_ptr(), 0, 1100, 4, 1100, t.data_ptr(), t.data_ptr(), 4, 0, 0, 1, 1.0, 0, 0, 0,
                                      t.data_ptr(), _stream()) == -2
     assert lib.b200vq_scores_partial(t.data_ptr(), 0, 16, 4, 16, t.data_ptr(), t.data_ptr(), 4, 4, 2, 1, 1.0, 0, 0, 0,
                                      t.data_ptr(), _stream()) == -3

@@ -10,9 +10,10 @@ from . import _lib, registry
 from .bottleneck import AbstractRegularizer, Bottleneck, SimpleVectorQuantizer, entropy_loss
 from .functional import codebook_lookup, prepare_codebook, usage_stats, vq_quantize
 from .registry import install, make, register
+from .simvq import SimVQ
 from .sq import VectorQuantizer
 
-__all__ = ["Bottleneck", "SimpleVectorQuantizer", "VectorQuantizer", "AbstractRegularizer", "entropy_loss", "vq_quantize",
+__all__ = ["Bottleneck", "SimpleVectorQuantizer", "VectorQuantizer", "SimVQ", "AbstractRegularizer", "entropy_loss", "vq_quantize",
            "codebook_lookup", "prepare_codebook", "usage_stats", "install", "make", "register", "registry",
            "load_library"]
 __version__ = "0.1.0"

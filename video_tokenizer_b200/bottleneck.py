@@ -100,8 +100,8 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         # B200 extras (accepted through **kwargs by the reference signature too)
         self.return_usage = bool(kwargs.get("return_usage", False))
         self.last_usage = None  # (hist_first, hist_batch) int32 (K,) of the last forward
-        if dim > 256:
-            raise ValueError(f"bottleneck dim {dim} > 256 is not supported by the B200 quantizer")
+        if dim > 1024:
+            raise ValueError(f"bottleneck dim {dim} > 1024 is not supported by the B200 quantizer")
 
     def set_eval_deterministic(self, deterministic=True):
         self.eval_deterministic = deterministic

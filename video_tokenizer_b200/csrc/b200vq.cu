@@ -162,7 +162,8 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
             });
         });
     } else {
-        const int64_t row_tiles = (N + 63) / 64;
+        const int rows = D <= 512 ? 64 : 32;   // rows per CTA: [rows][D+1] floats of shared memory (<= 131 KB)
+        const int64_t row_tiles = (N + rows - 1) / rows;
         const int64_t want = 8ll * sm_count();
         int64_t splits = std::max<int64_t>(1, (want + row_tiles - 1) / row_tiles);
         splits = std::min<int64_t>(splits, (K_local + 63) / 64);
@@ -170,13 +171,13 @@ int b200vq_scores_partial(const void* z, int z_dtype, int64_t z_row_stride, int6
         per = (per + 7) / 8 * 8;
         splits = (K_local + per - 1) / per;
         dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
-        const size_t smem = static_cast<size_t>(64) * (D + 1) * sizeof(float);
+        const size_t smem = static_cast<size_t>(rows) * (D + 1) * sizeof(float);
         B200VQ_DISPATCH_DTYPE(z_dtype, T, {
             B200VQ_DISPATCH_MODE(mode, MM, {
                 if (smem > 48 * 1024)
                     cudaFuncSetAttribute(scores_generic_kernel<T, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
-                scores_generic_kernel<T, MM><<<grid, 64, smem, st>>>(static_cast<const T*>(z), z_row_stride, N, D, emb,
+                scores_generic_kernel<T, MM><<<grid, rows, smem, st>>>(static_cast<const T*>(z), z_row_stride, N, D, emb,
                                                                      e2, K_local, k_offset, per, l2norm, t_inv, seed,
                                                                      offset, row_offset, k64);
             });

@@ -10,7 +10,7 @@
 namespace b200vq {
 
 constexpr float kNormEps = 1e-12f;  // F.normalize eps (reference bottleneck.py:255,267)
-constexpr int kMaxDim = 256;
+constexpr int kMaxDim = 1024;
 
 // ---- element loads --------------------------------------------------------------------
 template <int DT> struct ElemT;

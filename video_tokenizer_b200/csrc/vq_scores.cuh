@@ -178,8 +178,8 @@ __global__ void __launch_bounds__(64) scores_generic_kernel(const T* __restrict_
                                                             int64_t k_offset, int64_t codes_per_split, int l2norm,
                                                             float t_inv, uint64_t seed, uint64_t offset,
                                                             int64_t row_offset, unsigned long long* __restrict__ keys) {
-    extern __shared__ float s_z[];  // [64][D+1]
-    const int64_t row = static_cast<int64_t>(blockIdx.x) * 64 + threadIdx.x;
+    extern __shared__ float s_z[];  // [blockDim.x][D+1]
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (row >= N) return;
     float* zn = s_z + threadIdx.x * (D + 1);
     const T* zr = z + row * z_row_stride;
