@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 109
+#define B200VQ_VERSION 110
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -321,13 +321,16 @@ int b200vq_pack3(const float* a, const float* b, const float* c, float* out3, b2
  * l2_normalized, i.e. 'unregularized_z'); emb (K,D): 'emb'; both fp32, contiguous, 16-byte aligned; t_inv = 1/T_e.
  *   forward : out3 = {loss_entropy, per_sample_entropy, codebook_entropy};  saves lse (N), ent (N) =
  *             sum_k p log p per row, w (K) = d codebook_entropy / d mean-prob; psum (K) and ent_sum (1 double)
- *             are scratch.
+ *             are scratch; `scratch` (>= b200vq_entropy_scratch_bytes(N,K), 16-byte aligned) holds the per-split
+ *             row statistics when few rows meet many codes and the code stream is split across CTAs.
  *   backward: g3 = device {g_loss_entropy, g_per_sample_entropy, g_codebook_entropy}; c (N) scratch;
  *             grad_z (N,D) / grad_emb (K,D) written (each nullable = not needed).
  * b200vq_entropy_supported(D): D in {8,16,24,32}. */
 int b200vq_entropy_supported(int D);
+size_t b200vq_entropy_scratch_bytes(int64_t N, int64_t K);
 int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv, float* lse,
-                           float* ent, float* psum, float* w, double* ent_sum, float* out3, b200vq_stream_t stream);
+                           float* ent, float* psum, float* w, double* ent_sum, float* out3, void* scratch,
+                           size_t scratch_bytes, b200vq_stream_t stream);
 int b200vq_entropy_backward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv,
                             const float* lse, const float* ent, const float* w, const float* g3, float* c,
                             float* grad_z, float* grad_emb, b200vq_stream_t stream);

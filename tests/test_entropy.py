@@ -95,10 +95,11 @@ def test_entropy_dropin_matches_reference_golden(name):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("N,K,D,T", [(1, 8, 8, 0.5), (127, 65, 16, 0.05), (300, 2049, 24, 0.01), (4096, 8192, 24, 0.01),
-                                     (513, 129, 32, 0.1)])
+                                     (513, 129, 32, 0.1), (40000, 300, 16, 0.05), (200, 40000, 8, 0.05)])
 def test_entropy_kernels_match_closed_form(N, K, D, T):
-    """the kernels alone (ragged N and K, single row, the config-1 size) against the float64 closed form,
-    with separate upstream gradients on the three outputs"""
+    """the kernels alone (ragged N and K, single row, the config-1 size; split code streams, one and two owner
+    vectors per thread on either side) against the float64 closed form, with separate upstream gradients on the
+    three outputs"""
     from video_tokenizer_b200 import functional as VF
     gen = torch.Generator().manual_seed(N * 7 + K)
     z = torch.nn.functional.normalize(torch.randn(N, D, generator=gen), dim=-1)

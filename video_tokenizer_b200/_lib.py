@@ -53,7 +53,8 @@ SIGNATURES = {
     "b200vq_decode_project": (_i32, [_vp, _i64, _vp, _i64, _i32, _i32, _vp, _vp, _i32, _vp, _i64, _vp, _i64, _vp, _vp]),
     "b200vq_pack3": (_i32, [_vp, _vp, _vp, _vp, _vp]),
     "b200vq_entropy_supported": (_i32, [_i32]),
-    "b200vq_entropy_forward": (_i32, [_vp, _i64, _i32, _vp, _i64, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200vq_entropy_scratch_bytes": (_sz, [_i64, _i64]),
+    "b200vq_entropy_forward": (_i32, [_vp, _i64, _i32, _vp, _i64, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b200vq_entropy_backward": (_i32, [_vp, _i64, _i32, _vp, _i64, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200vq_grad_out_supported": (_i32, [_i32, _i32]),
     "b200vq_grad_out": (_i32, [_vp, _i64, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -238,9 +238,11 @@ class _EntropyFunction(torch.autograd.Function):
             w = torch.empty(K, **f32)
             ent_sum = torch.empty(1, dtype=torch.float64, device=dev)
             out3 = torch.empty(3, **f32)
+            nscr = lib.b200vq_entropy_scratch_bytes(N, K)
+            scr = torch.empty(max(nscr, 16), dtype=torch.uint8, device=dev)
             rc = lib.b200vq_entropy_forward(zz.data_ptr(), N, D, ee.data_ptr(), K, float(t_inv), lse.data_ptr(),
                                             ent.data_ptr(), psum.data_ptr(), w.data_ptr(), ent_sum.data_ptr(),
-                                            out3.data_ptr(), _stream())
+                                            out3.data_ptr(), scr.data_ptr(), nscr, _stream())
             _lib.check(rc, "b200vq_entropy_forward")
         ctx.save_for_backward(zz, ee, lse, ent, w)
         ctx.cfg = (float(t_inv), N, D, K, tuple(znorm.shape), tuple(emb.shape))
