@@ -43,11 +43,17 @@ def parse():
     p.add_argument("--mode", default="stochastic", choices=["stochastic", "deterministic"])
     p.add_argument("--cpu-batch", type=int, default=4, help="clips in the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    return p.parse_args()
+    p.add_argument("--dim", type=int, default=CFG["D"], choices=[8, 16, 24, 32],
+                   help="bottleneck_dim: 24 = cfgs/larp_tokenizer.yaml (the headline), 16 = larp_tokenizerf256t1024.yaml / "
+                        "larp_tokenizer_large.yaml (BASELINE configs[2], [3])")
+    args = p.parse_args()
+    CFG["D"] = args.dim
+    return args
 
 
 def workload_name(args, batch):
-    return (f"Bottleneck fwd+bwd, cfgs/larp_tokenizer.yaml block (C={CFG['C']}, D={CFG['D']}, K={CFG['K']}, "
+    yaml = "cfgs/larp_tokenizer.yaml" if CFG["D"] == 24 else ("cfgs/larp_tokenizerf256t1024.yaml" if CFG["D"] == 16 else "custom")
+    return (f"Bottleneck fwd+bwd, {yaml} block (C={CFG['C']}, D={CFG['D']}, K={CFG['K']}, "
             f"l2, {'stochastic T=0.03 train' if args.mode == 'stochastic' else 'deterministic argmin'}), "
             f"{batch}x{CFG['n']} tokens/GPU/step, fp32")
 
@@ -363,7 +369,7 @@ def run_b200(args):
     traffic = None   # dram bytes per launch of the same kernel from the committed ncu --set full capture
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r01c_traffic.json")))["tc_scores_kernel"]
-        if N == 65536 and args.mode == "stochastic":
+        if N == 65536 and D == 24 and args.mode == "stochastic":
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
     except Exception:
         traffic = None
