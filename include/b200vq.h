@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 110
+#define B200VQ_VERSION 111
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -325,7 +325,7 @@ int b200vq_pack3(const float* a, const float* b, const float* c, float* out3, b2
  *             row statistics when few rows meet many codes and the code stream is split across CTAs.
  *   backward: g3 = device {g_loss_entropy, g_per_sample_entropy, g_codebook_entropy}; c (N) scratch;
  *             grad_z (N,D) / grad_emb (K,D) written (each nullable = not needed).
- * b200vq_entropy_supported(D): D in {8,16,24,32}. */
+ * b200vq_entropy_supported(D): D in {8,16,24,32,64}. */
 int b200vq_entropy_supported(int D);
 size_t b200vq_entropy_scratch_bytes(int64_t N, int64_t K);
 int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, int64_t K, float t_inv, float* lse,

@@ -95,7 +95,8 @@ def test_entropy_dropin_matches_reference_golden(name):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("N,K,D,T", [(1, 8, 8, 0.5), (127, 65, 16, 0.05), (300, 2049, 24, 0.01), (4096, 8192, 24, 0.01),
-                                     (513, 129, 32, 0.1), (40000, 300, 16, 0.05), (200, 40000, 8, 0.05)])
+                                     (513, 129, 32, 0.1), (40000, 300, 16, 0.05), (200, 40000, 8, 0.05),
+                                     (300, 513, 64, 0.05)])
 def test_entropy_kernels_match_closed_form(N, K, D, T):
     """the kernels alone (ragged N and K, single row, the config-1 size; split code streams, one and two owner
     vectors per thread on either side) against the float64 closed form, with separate upstream gradients on the
@@ -140,7 +141,7 @@ def test_entropy_streamed_equals_torch_formulation_on_device():
 def test_entropy_unsupported_dim_uses_the_matrix_formulation():
     import video_tokenizer_b200 as V
     from video_tokenizer_b200 import functional as VF
-    assert not VF.entropy_supported(64) and not VF.entropy_supported(12)
-    m = V.SimpleVectorQuantizer(dim=64, codebook_size=50, l2_normalized=True, entropy_loss_weight=0.1).cuda()
-    out = m(torch.randn(1, 10, 64, device="cuda"))
+    assert VF.entropy_supported(64) and not VF.entropy_supported(12) and not VF.entropy_supported(128)
+    m = V.SimpleVectorQuantizer(dim=12, codebook_size=50, l2_normalized=True, entropy_loss_weight=0.1).cuda()
+    out = m(torch.randn(1, 10, 12, device="cuda"))
     assert torch.isfinite(out["loss_entropy"])

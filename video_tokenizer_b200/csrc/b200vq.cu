@@ -893,6 +893,9 @@ int launch_entropy_r(int D, const EntropyArgs& a, dim3 grid, cudaStream_t st) {
         case 16: entropy_pass_kernel<16, PASS, R><<<grid, kEntThreads, 0, st>>>(a); break;
         case 24: entropy_pass_kernel<24, PASS, R><<<grid, kEntThreads, 0, st>>>(a); break;
         case 32: entropy_pass_kernel<32, PASS, R><<<grid, kEntThreads, 0, st>>>(a); break;
+        case 64:   // one owner vector per thread only: two would not fit the register file (entropy_plan)
+            if constexpr (R == 1) { entropy_pass_kernel<64, PASS, 1><<<grid, kEntThreads, 0, st>>>(a); break; }
+            return B200VQ_EDIM;
         default: return B200VQ_EDIM;
     }
     return launch_check();
@@ -902,12 +905,12 @@ inline int64_t round_tile(int64_t v) { return (v + kEntTile - 1) / kEntTile * kE
 // Work split of one pass: owners per thread (2 whenever owners x splits can still fill the machine), CTAs over the
 // owners, and splits of the streamed side up to ~8 CTAs per SM (each split keeps >= 4 tiles).
 struct EntPlan { int own; dim3 grid; int64_t per; };
-inline EntPlan entropy_plan(int64_t n_own, int64_t n_str) {
+inline EntPlan entropy_plan(int64_t n_own, int64_t n_str, int D) {
     EntPlan pl;
     const int64_t sms = sm_count();
     const int64_t max_splits = std::max<int64_t>(1, n_str / (4 * kEntTile));
     const int64_t gx2 = (n_own + 2 * kEntThreads - 1) / (2 * kEntThreads);
-    pl.own = gx2 * max_splits >= sms ? 2 : 1;
+    pl.own = (D <= 32 && gx2 * max_splits >= sms) ? 2 : 1;
     const int64_t gx = (n_own + pl.own * kEntThreads - 1) / (pl.own * kEntThreads);
     // ~8 CTAs per SM measured best on B200 (profiles/r01g_summary.md): the passes are issue-latency bound, and a split
     // only costs one atomic per output element (or the ROWSTATS merge)
@@ -928,11 +931,12 @@ int launch_entropy(int D, EntropyArgs& a, const EntPlan& pl, cudaStream_t st) {
 
 extern "C" {
 
-int b200vq_entropy_supported(int D) { return (D == 8 || D == 16 || D == 24 || D == 32) ? 1 : 0; }
+int b200vq_entropy_supported(int D) { return (D == 8 || D == 16 || D == 24 || D == 32 || D == 64) ? 1 : 0; }
 
 size_t b200vq_entropy_scratch_bytes(int64_t N, int64_t K) {
     if (N <= 0 || K <= 0) return 0;
-    const EntPlan pl = entropy_plan(N, K);
+    // upper bound over D: two owners per thread give the fewest owner CTAs, hence the most splits
+    const EntPlan pl = entropy_plan(N, K, 8);
     return align_up(static_cast<size_t>(pl.grid.y) * static_cast<size_t>(N) * 3 * sizeof(float));
 }
 
@@ -949,7 +953,7 @@ int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, i
     if ((rc = cuda_check(cudaMemsetAsync(ent_sum, 0, sizeof(double), st)))) return rc;
     const float inv_n = 1.0f / static_cast<float>(N);
     // rows own, codes stream: lse_i, ent_i, sum of ent
-    const EntPlan rows = entropy_plan(N, K);
+    const EntPlan rows = entropy_plan(N, K, D);
     EntropyArgs a{};
     a.t_inv = t_inv;
     a.inv_n = inv_n;
@@ -970,7 +974,7 @@ int b200vq_entropy_forward(const float* z, int64_t N, int D, const float* emb, i
     b.t_inv = t_inv;
     b.inv_n = inv_n;
     b.own = emb; b.n_own = K; b.str = z; b.n_str = N; b.str_a = lse; b.out_a = psum;
-    if ((rc = launch_entropy<ENT_COLSUM>(D, b, entropy_plan(K, N), st))) return rc;
+    if ((rc = launch_entropy<ENT_COLSUM>(D, b, entropy_plan(K, N, D), st))) return rc;
     entropy_finalize_kernel<<<1, 1024, 0, st>>>(psum, K, inv_n, ent_sum, w, out3);
     return launch_check();
 }
@@ -985,7 +989,7 @@ int b200vq_entropy_backward(const float* z, int64_t N, int D, const float* emb, 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc;
     const float inv_n = 1.0f / static_cast<float>(N);
-    const EntPlan rows = entropy_plan(N, K);
+    const EntPlan rows = entropy_plan(N, K, D);
     EntropyArgs a{};
     a.t_inv = t_inv;
     a.inv_n = inv_n;
@@ -1007,7 +1011,7 @@ int b200vq_entropy_backward(const float* z, int64_t N, int D, const float* emb, 
         b.inv_n = inv_n;
         b.own = emb; b.n_own = K; b.str = z; b.n_str = N;
         b.own_a = w; b.str_a = lse; b.str_b = ent; b.str_c = c; b.g3 = g3; b.out_vec = grad_emb;
-        if ((rc = launch_entropy<ENT_GRAD_CODES>(D, b, entropy_plan(K, N), st))) return rc;
+        if ((rc = launch_entropy<ENT_GRAD_CODES>(D, b, entropy_plan(K, N, D), st))) return rc;
     }
     return B200VQ_OK;
 }
