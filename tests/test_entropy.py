@@ -117,13 +117,15 @@ def test_entropy_kernels_match_closed_form(N, K, D, T):
 
 
 @pytest.mark.gpu
-def test_entropy_streamed_equals_torch_formulation_on_device():
-    """same device, same tensors: the streaming kernels against the reference's N x K op sequence in torch"""
+@pytest.mark.parametrize("N,K,D", [(2000, 1000, 24), (65536, 8192, 24)])
+def test_entropy_streamed_equals_torch_formulation_on_device(N, K, D):
+    """same device, same tensors: the streaming kernels against the reference's N x K op sequence in torch
+    (the second case is BASELINE's full bench size: 64 x 1024 tokens, K = 8192 -- 2 GiB per matrix for torch)"""
     import video_tokenizer_b200 as V
     from video_tokenizer_b200 import functional as VF
     torch.manual_seed(5)
-    z = torch.nn.functional.normalize(torch.randn(2000, 24), dim=-1).cuda()
-    e = torch.nn.functional.normalize(torch.randn(1000, 24), dim=-1).cuda()
+    z = torch.nn.functional.normalize(torch.randn(N, D), dim=-1).cuda()
+    e = torch.nn.functional.normalize(torch.randn(K, D), dim=-1).cuda()
     z1, e1 = z.clone().requires_grad_(True), e.clone().requires_grad_(True)
     z2, e2 = z.clone().requires_grad_(True), e.clone().requires_grad_(True)
     a = VF.entropy_loss_streamed(z1, e1, 0.01)
