@@ -1,0 +1,165 @@
+// b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
+// This unit: the tcgen05 tensor-core scoring path.
+#include "vq_tc_kernel.cuh"
+#include "b200vq_host.h"
+
+using namespace b200vq;
+using namespace b200vq::host;
+
+namespace {
+template <int DD, typename T, int MM>
+int launch_tc(const TcParams& prm, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = tc_smem_bytes<DD>();
+    if (int rc = set_smem(tc_scores_kernel<DD, T, MM>, smem)) return rc;   // per device: set on every launch
+    tc_scores_kernel<DD, T, MM><<<grid, kTcThreads, smem, st>>>(prm);
+    return launch_check();
+}
+}  // namespace
+
+extern "C" {
+
+// ---- tensor-core path --------------------------------------------------------------------------
+size_t b200vq_tc_scratch_bytes(int64_t N) {
+    // [runner-up scores: N f32][undecided-row list: count + 3 pad, N u32]; the caller zeroes it
+    return N < 0 ? 0 : static_cast<size_t>(N) * 8 + 16;
+}
+
+int b200vq_tc_supported(int D, int l2norm, int mode) {
+    return tc_dim_ok(D) && l2norm && valid_mode(mode) ? 1 : 0;
+}
+
+size_t b200vq_tc_image_bytes(int64_t K, int D) {
+    if (K <= 0 || !tc_dim_ok(D)) return 0;
+    // tiles, then one 16-byte trailer holding the "codebook has a non-unit row" flag word
+    return static_cast<size_t>((K + kTcCodes - 1) / kTcCodes) * tc_tile_bytes(D) + 16;
+}
+
+int b200vq_prepare_codebook_tc(const float* emb, int64_t K, int D, void* image, b200vq_stream_t stream) {
+    if (!emb || !image || K <= 0) return B200VQ_EINVAL;
+    if (!tc_dim_ok(D)) return B200VQ_EDIM;
+    if (reinterpret_cast<uintptr_t>(image) & 15) return B200VQ_EALIGN;
+    const unsigned blocks = static_cast<unsigned>((K + kTcCodes - 1) / kTcCodes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint4* img = static_cast<uint4*>(image);
+    unsigned int* flags = reinterpret_cast<unsigned int*>(static_cast<char*>(image) + static_cast<size_t>(blocks) * tc_tile_bytes(D));
+    int rc = cuda_check(cudaMemsetAsync(flags, 0, 16, st));
+    if (rc) return rc;
+    switch (D) {
+        case 8: prepare_codebook_tc_kernel<8><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        case 16: prepare_codebook_tc_kernel<16><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        case 24: prepare_codebook_tc_kernel<24><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+        default: prepare_codebook_tc_kernel<32><<<blocks, kTcCodes, 0, st>>>(emb, K, img, flags); break;
+    }
+    return launch_check();
+}
+
+
+int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const void* image,
+                     const float* emb, const float* e2, int64_t K, int64_t k_offset, int mode, int l2norm,
+                     float t_inv, uint64_t seed, uint64_t offset, int64_t row_offset, uint64_t* keys, float* scratch,
+                     unsigned int* n_resolved, b200vq_stream_t stream) {
+    if (N < 0 || K <= 0 || k_offset < 0 || row_offset < 0 || !valid_dtype(z_dtype) || !valid_mode(mode)) return B200VQ_EINVAL;
+    if (!tc_dim_ok(D)) return B200VQ_EDIM;
+    if (!l2norm) return B200VQ_EINVAL;  // the error bound assumes unit vectors
+    if (N == 0) return B200VQ_OK;
+    if (!z || !image || !keys || z_row_stride < D) return B200VQ_EINVAL;
+    if (mode != B200VQ_MODE_SAMPLE && (!emb || !e2 || !scratch)) return B200VQ_EINVAL;
+    if (k_offset & (kTcCodes - 1)) return B200VQ_EALIGN;
+    if (k_offset + K > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t row_tiles = (N + kTcRows - 1) / kTcRows;
+    const int total_tiles = static_cast<int>((K + kTcCodes - 1) / kTcCodes);
+    // code splits: fill the SMs, keep the last wave full, keep >= 4 tiles per CTA when possible
+    const int sms = sm_count();
+    int best_splits = 1;
+    double best_cost = 1e30;
+    for (int sp = 1; sp <= total_tiles; sp *= 2) {
+        const int per = (total_tiles + sp - 1) / sp;
+        if (sp > 1 && per < 4) break;
+        const int real = (total_tiles + per - 1) / per;
+        const double ctas = static_cast<double>(row_tiles) * real;
+        // measured (tools/tc_probe.py): a CTA costs ~6.5 tiles of prologue/teardown on top of its tiles,
+        // and CTAs of later waves start as soon as an SM frees up
+        const double waves = ctas <= sms ? 1.0 : ctas / sms;
+        const double cost = waves * (per + 6.5);
+        if (cost < best_cost) { best_cost = cost; best_splits = sp; }
+    }
+    if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
+        const int v = std::atoi(env);
+        if (v >= 1 && v <= total_tiles) best_splits = v;
+    }
+    const int per = (total_tiles + best_splits - 1) / best_splits;
+    const int splits = (total_tiles + per - 1) / per;
+    TcParams prm;
+    prm.z = z; prm.z_row_stride = z_row_stride; prm.N = N; prm.image = static_cast<const uint4*>(image);
+    prm.K = K; prm.k_offset = k_offset; prm.tiles_per_split = per; prm.l2norm = l2norm; prm.t_inv = t_inv;
+    prm.seed = seed; prm.offset = offset; prm.row_offset = row_offset;
+    prm.keys = reinterpret_cast<unsigned long long*>(keys); prm.second = scratch;
+    prm.debug = 0;
+    prm.n_events = mode == B200VQ_MODE_SAMPLE ? n_resolved : nullptr;
+    if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
+    dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+    int rc = B200VQ_OK;
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        switch (D) {
+            case 8: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<8, T, MM>(prm, grid, st); }); break; }
+            case 16: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<16, T, MM>(prm, grid, st); }); break; }
+            case 24: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<24, T, MM>(prm, grid, st); }); break; }
+            default: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<32, T, MM>(prm, grid, st); }); break; }
+        }
+    });
+    if (rc || mode == B200VQ_MODE_SAMPLE || prm.debug) return rc;
+    // exact re-scoring of undecided rows (deterministic modes)
+    const unsigned int* flags = reinterpret_cast<const unsigned int*>(
+        static_cast<const char*>(image) + static_cast<size_t>(total_tiles) * tc_tile_bytes(D));
+    unsigned long long* k64 = reinterpret_cast<unsigned long long*>(keys);
+    unsigned int* list = reinterpret_cast<unsigned int*>(scratch + N);
+#define B200VQ_GROUPS(DD, MM)                                                                                  \
+    resolve_groups_kernel<DD, T, MM><<<static_cast<unsigned>((N + kResolveRows - 1) / kResolveRows), 256, 0, st>>>(                      \
+        static_cast<const T*>(z), z_row_stride, N, emb, e2, K, k_offset, l2norm, k64, scratch, flags, list)
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        if (mode == B200VQ_MODE_ARGMIN_DIST) {
+            switch (D) {
+                case 8: B200VQ_GROUPS(8, B200VQ_MODE_ARGMIN_DIST); break;
+                case 16: B200VQ_GROUPS(16, B200VQ_MODE_ARGMIN_DIST); break;
+                case 24: B200VQ_GROUPS(24, B200VQ_MODE_ARGMIN_DIST); break;
+                default: B200VQ_GROUPS(32, B200VQ_MODE_ARGMIN_DIST); break;
+            }
+        } else {
+            switch (D) {
+                case 8: B200VQ_GROUPS(8, B200VQ_MODE_ARGMAX_COS); break;
+                case 16: B200VQ_GROUPS(16, B200VQ_MODE_ARGMAX_COS); break;
+                case 24: B200VQ_GROUPS(24, B200VQ_MODE_ARGMAX_COS); break;
+                default: B200VQ_GROUPS(32, B200VQ_MODE_ARGMAX_COS); break;
+            }
+        }
+    });
+#undef B200VQ_GROUPS
+    rc = launch_check();
+    if (rc) return rc;
+    const unsigned rblocks = static_cast<unsigned>(kRescoreSegs * std::min<int64_t>(N, 2ll * sms));
+#define B200VQ_RESOLVE(DD, MM)                                                                                \
+    rescore_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, emb, e2, K,    \
+                                                        k_offset, l2norm, k64, list, n_resolved)
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        if (mode == B200VQ_MODE_ARGMIN_DIST) {
+            switch (D) {
+                case 8: B200VQ_RESOLVE(8, B200VQ_MODE_ARGMIN_DIST); break;
+                case 16: B200VQ_RESOLVE(16, B200VQ_MODE_ARGMIN_DIST); break;
+                case 24: B200VQ_RESOLVE(24, B200VQ_MODE_ARGMIN_DIST); break;
+                default: B200VQ_RESOLVE(32, B200VQ_MODE_ARGMIN_DIST); break;
+            }
+        } else {
+            switch (D) {
+                case 8: B200VQ_RESOLVE(8, B200VQ_MODE_ARGMAX_COS); break;
+                case 16: B200VQ_RESOLVE(16, B200VQ_MODE_ARGMAX_COS); break;
+                case 24: B200VQ_RESOLVE(24, B200VQ_MODE_ARGMAX_COS); break;
+                default: B200VQ_RESOLVE(32, B200VQ_MODE_ARGMAX_COS); break;
+            }
+        }
+    });
+#undef B200VQ_RESOLVE
+    return launch_check();
+}
+
+}  // extern "C"

@@ -16,7 +16,7 @@ namespace b200vq {
 // =======================================================================================
 // Codebook preparation: get_emb (bottleneck.py:252-259).  One warp per code row.
 // =======================================================================================
-__global__ void __launch_bounds__(256) prepare_codebook_kernel(const float* __restrict__ w, int64_t K, int D,
+static __global__ void __launch_bounds__(256) prepare_codebook_kernel(const float* __restrict__ w, int64_t K, int D,
                                                                int l2norm, float* __restrict__ emb,
                                                                float* __restrict__ e2, float* __restrict__ wnorm) {
     const int lane = threadIdx.x & 31;
