@@ -1,6 +1,6 @@
 // b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
 // This unit: the tcgen05 tensor-core scoring path.
-#include "vq_tc_kernel.cuh"
+#include "vq_tc_sample.cuh"
 #include "b200vq_host.h"
 
 using namespace b200vq;
@@ -13,6 +13,17 @@ int launch_tc(const TcParams& prm, dim3 grid, cudaStream_t st) {
     if (int rc = set_smem(tc_scores_kernel<DD, T, MM>, smem)) return rc;   // per device: set on every launch
     tc_scores_kernel<DD, T, MM><<<grid, kTcThreads, smem, st>>>(prm);
     return launch_check();
+}
+template <int DD, typename T>
+int launch_ts(const TsParams& prm, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = ts_smem_bytes<DD>();
+    if (int rc = set_smem(tc_sample_kernel<DD, T>, smem)) return rc;
+    tc_sample_kernel<DD, T><<<grid, kTcThreads, smem, st>>>(prm);
+    return launch_check();
+}
+inline int env_int(const char* name, int fallback) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : fallback;
 }
 }  // namespace
 
@@ -63,7 +74,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     if (!l2norm) return B200VQ_EINVAL;  // the error bound assumes unit vectors
     if (N == 0) return B200VQ_OK;
     if (!z || !image || !keys || z_row_stride < D) return B200VQ_EINVAL;
-    if (mode != B200VQ_MODE_SAMPLE && (!emb || !e2 || !scratch)) return B200VQ_EINVAL;
+    if (!emb || (mode != B200VQ_MODE_SAMPLE && (!e2 || !scratch))) return B200VQ_EINVAL;
     if (k_offset & (kTcCodes - 1)) return B200VQ_EALIGN;
     if (k_offset + K > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -100,6 +111,29 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
     int rc = B200VQ_OK;
+    static const bool old_sampler = std::getenv("B200VQ_TS_OLD") != nullptr;   // tuning aid: the first-generation sampler
+    if (mode == B200VQ_MODE_SAMPLE && !old_sampler) {
+        // second-generation sampler (vq_tc_sample.cuh): bf16 filter + exact expansion of the candidates
+        TsParams ts;
+        ts.z = z; ts.z_row_stride = z_row_stride; ts.N = N; ts.image = static_cast<const uint8_t*>(image); ts.emb = emb;
+        ts.K = K; ts.k_offset = k_offset; ts.tiles_per_split = per; ts.l2norm = l2norm; ts.t_inv = t_inv;
+        ts.seed = seed; ts.offset = offset; ts.row_offset = row_offset;
+        ts.keys = reinterpret_cast<unsigned long long*>(keys); ts.n_events = n_resolved; ts.debug = prm.debug;
+        // warm start: scan the first eighth of the CTA's tiles for the row's best group before testing
+        ts.scout_tiles = std::min(per, std::max(0, env_int("B200VQ_TS_SCOUT", per >= 16 ? per / 8 : (per >= 8 ? 1 : 0))));
+        ts.flush_early = std::max(1, env_int("B200VQ_TS_FLUSH_EARLY", 8));
+        ts.flush_late = std::max(1, env_int("B200VQ_TS_FLUSH_LATE", 32));
+        ts.early_iters = env_int("B200VQ_TS_EARLY_ITERS", 2);
+        B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+            switch (D) {
+                case 8: rc = launch_ts<8, T>(ts, grid, st); break;
+                case 16: rc = launch_ts<16, T>(ts, grid, st); break;
+                case 24: rc = launch_ts<24, T>(ts, grid, st); break;
+                default: rc = launch_ts<32, T>(ts, grid, st); break;
+            }
+        });
+        return rc;
+    }
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
         switch (D) {
             case 8: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<8, T, MM>(prm, grid, st); }); break; }

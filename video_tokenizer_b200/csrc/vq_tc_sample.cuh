@@ -1,0 +1,400 @@
+// b200vq -- tcgen05 stochastic (SVQ) scoring kernel, second generation.
+//
+// Reference semantics: idx ~ multinomial(softmax(cos / T))  (models/bottleneck.py:275-280), drawn here as a
+// Gumbel-max over the streamed scores with the per-(row, code) noise of vq_common.cuh, so the draw is
+// bit-identical to the exact-fp32 kernel's (vq_scores.cuh) for the same (seed, offset).
+//
+// What changed against the first sampler (vq_tc_kernel.cuh, MODE_SAMPLE):
+//   * the tensor core only FILTERS.  Scores come from ONE bf16 product (z_hi . e_hi: 2 MMAs per 256-code tile
+//     at D = 24 instead of 5), whose error is at most 2^-8 for unit vectors (two 2^-9 roundings, Cauchy-Schwarz).
+//     A group of 8 codes is skipped only if   (max score + 2^-8) / T + (largest Gumbel its 16 head bits allow)
+//     cannot beat the row's best perturbed score so far; that test is one FFMA per group and one compare per 32
+//     columns;
+//   * a group that passes is only QUEUED: (group id, row, head bits) + its 8 approximate scores as fp16, 24 bytes,
+//     slot from one shared-memory atomic, no ballots.  The warp expands 32 queued groups at a time, one per lane:
+//     the bound test is repeated per CODE against the row's CURRENT best (stale entries die here for a few
+//     instructions), and the codes that survive (usually one) are re-scored in exact fp32 from the fp32 codebook
+//     (same FMA order as scores_kernel), perturbed and merged into the row's key.  The final value of every
+//     candidate is therefore exact -- the approximate scores never reach the result;
+//   * warm start.  A running maximum over K/8 groups sees ~e^(lambda*slack) * ln(K/8) near-records.  The first
+//     `scout` tiles are first only SCANNED for the row's best approximate group (no tests); that one group is
+//     expanded, which puts the row's threshold within a couple of nats of its final value; then the remaining
+//     tiles are tested, and the scout tiles are run again (tested) at the end.  Costs scout/ntiles more MMA
+//     work, removes most of the early candidates.
+//
+// CTA layout as in vq_tc_kernel.cuh: 128 rows x a range of 256-code tiles; warps 0-15 = four epilogue groups
+// (TMEM buffer x column half), warp 16 = bulk-copy producer, warps 17/18 = MMA issuers of even / odd iterations.
+#pragma once
+#include "vq_tc_kernel.cuh"
+
+namespace b200vq {
+
+constexpr int kTsStages = 4;          // codebook tiles in flight
+constexpr int kTsQueueSlots = 256;    // per epilogue warp (ring): <= 31 left over + <= 128 pushed per chunk
+constexpr float kTsScoreEps = 4.2e-3f;    // 2^-8 + 2^-18 (bf16 operands, unit vectors) + 2^-12 (fp16 copy in the queue) + fp32 accumulation
+
+template <int D> __host__ __device__ constexpr int ts_chunks() { return 2 * ((D + 15) / 16); }   // 16-byte K chunks incl. zero padding
+template <int D> __host__ __device__ constexpr uint32_t ts_stage_bytes() { return ts_chunks<D>() * kTcCodes * 16; }
+template <int D> __host__ __device__ constexpr uint32_t ts_copy_bytes() { return (D / 8) * kTcCodes * 16; }  // the image's e_hi chunks
+template <int D> __host__ __device__ constexpr int ts_zstride() { return D + 4; }
+template <int D>
+__host__ __device__ constexpr size_t ts_smem_bytes() {
+    return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * ts_chunks<D>() * 16 + kTsStages * ts_stage_bytes<D>() +
+           static_cast<size_t>(kTcRows) * ts_zstride<D>() * 4 + static_cast<size_t>(kTcEpiWarps) * kTsQueueSlots * 24 +
+           kTcRows * 8 + 512;
+}
+
+// log2 of a 16-bit integer (exact conversion through the 2^23 trick; 0 -> -inf)
+__device__ __forceinline__ float lg2_u16(uint32_t h) { return lg2_approx(__uint_as_float(0x4B000000u | h) - 8388608.0f); }
+
+struct TsParams {
+    const void* z;
+    int64_t z_row_stride;
+    int64_t N;
+    const uint8_t* image;     // split-bf16 codebook image (prepare_codebook_tc_kernel); only the e_hi chunks are read
+    const float* emb;         // (K, D) fp32 normalised codebook rows of this slice (exact expansion)
+    int64_t K;                // codes in the slice
+    int64_t k_offset;         // global index of code 0 (multiple of 256)
+    int tiles_per_split;
+    int scout_tiles;          // tiles scanned for a warm-start group before testing (0 = none)
+    int l2norm;
+    float t_inv;
+    uint64_t seed, offset;
+    int64_t row_offset;
+    unsigned long long* keys; // (N) merged with atomicMax
+    unsigned int* n_events;   // nullable: += groups expanded (statistics)
+    int debug;                // tuning aid: 1 = no MMA, 2 = no epilogue work, 64 = candidates dropped
+    int flush_early, flush_late, early_iters;   // smallest batch drained at a tile end (first iterations / later)
+};
+
+// ---- expand up to 32 queued groups, one per lane.  Per code of the group the bound test is repeated against the
+// row's current best; surviving codes get their exact fp32 score (the arithmetic of scores_kernel), the group's
+// Gumbels are generated, and the best perturbed value is merged into the row's key ----------------------------
+template <int D>
+__device__ __noinline__ void ts_flush(const uint4* q_sc, const uint2* q_meta, uint32_t qhead, uint32_t n, uint32_t lane,
+                                      uint32_t row_base, const float* s_z, unsigned long long* s_key,
+                                      const float* __restrict__ emb, uint32_t k_offset, uint32_t k_end_global,
+                                      uint32_t grow0, float t_inv, float tl2e, float slack19, uint64_t seed,
+                                      uint64_t offset) {
+    if (lane < n) {
+        const uint32_t slot = (qhead + lane) & (kTsQueueSlots - 1);
+        const uint2 meta = q_meta[slot];
+        const uint4 sc = q_sc[slot];
+        const uint32_t group = meta.x, rl = row_base + (meta.y & 31u), hi16 = meta.y >> 16;
+        const float nthr = fmaf(key_value(s_key[rl]), kLog2e, -slack19);
+        const float lh = lg2_u16(hi16);
+        const uint32_t code0 = group * 8u;
+        const uint32_t w[4] = {sc.x, sc.y, sc.z, sc.w};
+        uint32_t live = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            live |= fmaf(f.x, tl2e, -lh) > nthr ? (1u << (2 * i)) : 0u;
+            live |= fmaf(f.y, tl2e, -lh) > nthr ? (2u << (2 * i)) : 0u;
+        }
+        if (code0 + 8u > k_end_global) live &= (1u << (k_end_global - code0)) - 1u;   // codes beyond the slice
+        if (live != 0u) {
+            float g[8];
+            group_noise(group, grow0 + rl, seed, offset, hi16, g);
+            float zn[D];
+            const float* zr = s_z + rl * ts_zstride<D>();
+#pragma unroll
+            for (int d = 0; d < D; d += 4) {
+                const float4 t = *reinterpret_cast<const float4*>(zr + d);
+                zn[d] = t.x; zn[d + 1] = t.y; zn[d + 2] = t.z; zn[d + 3] = t.w;
+            }
+            const float* e = emb + static_cast<size_t>(code0 - k_offset) * D;
+            float bv = -INFINITY;
+            uint32_t bk = code0;
+            while (live != 0u) {                     // ascending code order: ties keep the lowest index
+                const int pos = __ffs(live) - 1;
+                live &= live - 1u;
+                float acc = 0.f;
+#pragma unroll
+                for (int d = 0; d < D; d += 4) {
+                    const float4 ev = __ldg(reinterpret_cast<const float4*>(e + pos * D + d));
+                    acc = fmaf(zn[d + 0], ev.x, acc);
+                    acc = fmaf(zn[d + 1], ev.y, acc);
+                    acc = fmaf(zn[d + 2], ev.z, acc);
+                    acc = fmaf(zn[d + 3], ev.w, acc);
+                }
+                float gp = g[0];
+#pragma unroll
+                for (int t = 1; t < 8; ++t) gp = pos == t ? g[t] : gp;
+                const float v = __fmaf_rn(acc, t_inv, gp);
+                if (v > bv) { bv = v; bk = code0 + pos; }
+            }
+            atomicMax(s_key + rl, make_key(bv, bk));
+        }
+    }
+    __syncwarp();
+}
+
+// =======================================================================================
+// grid = (row tiles of 128, code splits); block = kTcThreads; dynamic smem = ts_smem_bytes<D>()
+// =======================================================================================
+template <int D, typename T>
+__global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams p) {
+    constexpr int CH = ts_chunks<D>();          // K chunks per operand row (incl. zero padding)
+    constexpr int P = D / 8;                    // real chunks
+    constexpr int SLABS = CH / 2;               // MMAs (K = 16) per tile
+    constexpr uint32_t A_BYTES = kTcRows * CH * 16;
+    constexpr uint32_t B_BYTES = ts_stage_bytes<D>();
+    constexpr uint32_t A_LBO = kTcRows * 16, B_LBO = kTcCodes * 16, SBO = 128;
+    constexpr int ZS = ts_zstride<D>();
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + A_BYTES;
+    float* s_z = reinterpret_cast<float*>(sB + kTsStages * B_BYTES);
+    uint4* s_qsc = reinterpret_cast<uint4*>(s_z + kTcRows * ZS);                      // queued groups: 8 fp16 scores
+    uint2* s_qmeta = reinterpret_cast<uint2*>(s_qsc + kTcEpiWarps * kTsQueueSlots);     // (group, lane | head << 16)
+    unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_qmeta + kTcEpiWarps * kTsQueueSlots);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_key + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTsStages + 2 * kTcBufs);
+    uint32_t* s_qtail = s_tmem + 4;   // (kTcEpiWarps) queue tails
+
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kTcRows;
+    const int total_tiles = static_cast<int>((p.K + kTcCodes - 1) / kTcCodes);
+    const int tile_begin = blockIdx.y * p.tiles_per_split;
+    const int ntiles = min(p.tiles_per_split, total_tiles - tile_begin);
+    const int scout = min(p.scout_tiles, ntiles);
+    const int iters = ntiles + scout;           // iteration j: tile j (scan only while j < scout), then tiles 0..scout-1 again
+    const uint32_t first_code = static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes;
+
+    const uint32_t bar_full = smem_u32(s_bar), bar_empty = bar_full + 8 * kTsStages;
+    const uint32_t bar_tfull = bar_empty + 8 * kTsStages, bar_tempty = bar_tfull + 8 * kTcBufs;
+
+    // ---- prologue ---------------------------------------------------------------------------------
+    if (threadIdx.x < kTcRows) {
+        const int64_t row = row0 + threadIdx.x;
+        float zn[D];
+        float z2, zlen;
+        if (row < p.N) {
+            load_normalised_row<D, T>(static_cast<const T*>(p.z) + row * p.z_row_stride, p.l2norm, zn, z2, zlen);
+        } else {
+#pragma unroll
+            for (int d = 0; d < D; ++d) zn[d] = 0.f;
+        }
+#pragma unroll
+        for (int d = 0; d < D; d += 4)
+            *reinterpret_cast<float4*>(s_z + threadIdx.x * ZS + d) = make_float4(zn[d], zn[d + 1], zn[d + 2], zn[d + 3]);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+            if (c < P) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const uint32_t a = __bfloat16_as_ushort(__float2bfloat16_rn(zn[c * 8 + 2 * e]));
+                    const uint32_t b = __bfloat16_as_ushort(__float2bfloat16_rn(zn[c * 8 + 2 * e + 1]));
+                    w[e] = a | (b << 16);
+                }
+            }
+            *reinterpret_cast<uint4*>(sA + c * A_LBO + threadIdx.x * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        s_key[threadIdx.x] = make_key(-INFINITY, first_code);
+        if (threadIdx.x < kTcEpiWarps) s_qtail[threadIdx.x] = 0u;
+    } else if (warp == kTcEpiWarps) {
+        if (lane == 0) {
+            for (int s = 0; s < kTsStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+            for (int b = 0; b < kTcBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 256); }
+            fence_barrier_init();
+        }
+    } else if (warp == kTcEpiWarps + 1) {
+        tmem_alloc(smem_u32(s_tmem), 512);
+    }
+    if constexpr (CH > P) {
+        // zero K-padding chunks of every codebook stage (the bulk copies only write chunks [0, P))
+        constexpr int PAD16 = (CH - P) * kTcCodes;   // 16-byte words per stage
+        for (int i = threadIdx.x; i < kTsStages * PAD16; i += kTcThreads) {
+            const int s = i / PAD16, o = i % PAD16;
+            *reinterpret_cast<uint4*>(sB + s * B_BYTES + P * B_LBO + o * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
+    fence_proxy_async();  // A tile / zero padding (generic-proxy stores) -> visible to the tensor core (async proxy)
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+
+    if (warp == kTcEpiWarps) {
+        // ===== codebook tile producer: one bulk copy (the e_hi chunks of the tile) per iteration ==============
+        if (lane == 0) {
+            const uint8_t* src = p.image + static_cast<size_t>(tile_begin) * tc_tile_bytes(D);
+            for (int j = 0; j < iters; ++j) {
+                const int s = j % kTsStages;
+                const int tile = j < ntiles ? j : j - ntiles;
+                mbar_wait(bar_empty + 8 * s, ((j / kTsStages) & 1) ^ 1);
+                mbar_expect_tx(bar_full + 8 * s, ts_copy_bytes<D>());
+                bulk_g2s(smem_u32(sB + s * B_BYTES), src + static_cast<size_t>(tile) * tc_tile_bytes(D), ts_copy_bytes<D>(),
+                         bar_full + 8 * s);
+            }
+        }
+    } else if (warp >= kTcEpiWarps + 1) {
+        // ===== MMA issuers: warp 17 issues the iterations of buffer 0, warp 18 those of buffer 1 ===============
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTcCodes);
+            const int buf = warp - (kTcEpiWarps + 1);
+            const uint32_t a0 = smem_u32(sA);
+            for (int j = buf; j < iters; j += kTcBufs) {
+                const int s = j % kTsStages;
+                mbar_wait(bar_tempty + 8 * buf, ((j / kTcBufs) & 1) ^ 1);
+                mbar_wait(bar_full + 8 * s, (j / kTsStages) & 1);
+                tc_fence_after();
+                const uint32_t b0 = smem_u32(sB + s * B_BYTES);
+#pragma unroll
+                for (int k = 0; k < SLABS; ++k) {
+                    if (p.debug & 1) break;
+                    umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
+                              umma_desc(b0 + k * 2 * B_LBO, B_LBO, SBO), idesc, k > 0);
+                }
+                umma_commit(bar_tfull + 8 * buf);   // the epilogue group that sees it also frees the codebook stage
+            }
+        }
+    } else {
+        // ===== epilogue groups: group g = warps 4g..4g+3, columns [128*(g&1), +128) of buffer g>>1 ==========
+        const int grp = warp >> 2, buf = grp >> 1, half = grp & 1;
+        const uint32_t row_base = 32u * (warp & 3);
+        const uint32_t row_local = row_base + lane;
+        uint4* q_sc = s_qsc + warp * kTsQueueSlots;
+        uint2* q_meta = s_qmeta + warp * kTsQueueSlots;
+        volatile uint32_t* qtail_p = s_qtail + warp;
+        uint32_t qhead = 0;   // warp-uniform
+        const uint32_t grow0 = static_cast<uint32_t>(p.row_offset + row0);
+        const uint32_t k_off32 = static_cast<uint32_t>(p.k_offset);
+        const uint32_t k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
+        const uint32_t t_lane = tmem_base + (row_base << 16) + buf * kTcCodes + half * 128;
+        const float tl2e = p.t_inv * kLog2e;
+        // candidate iff  m * tl2e - log2(head)  >  vstar * log2(e) - (19 + slack):   slack covers the score error
+        // (kTsScoreEps / T in log2 units) and the lg2 / FFMA rounding of the test itself
+        const float slack19 = 19.02f + kTsScoreEps * tl2e;
+        auto read_nthr = [&]() { return fmaf(key_value(s_key[row_local]), kLog2e, -slack19); };
+        auto flush = [&](uint32_t n) {
+            ts_flush<D>(q_sc, q_meta, qhead, n, lane, row_base, s_z, s_key, p.emb, k_off32, k_end_global, grow0, p.t_inv, tl2e,
+                        slack19, p.seed, p.offset);
+            qhead += n;
+        };
+        float nthr = -INFINITY;      // "everything can matter" until the row has a key
+        float sbest = -INFINITY;     // scout: best tagged group maximum, and the first group of its 32-column chunk
+        uint32_t sgrp = first_code >> 3;
+        uint32_t va[32];
+        Philox4 r0{}, r1{};          // 16 random bits per group: the heads of this thread's 16 groups of the tile
+        int tested = 0;
+        for (int j = buf; j < iters; j += kTcBufs) {
+            const bool scan_only = j < scout;
+            const int tile = j < ntiles ? j : j - ntiles;
+            const int64_t code0 = static_cast<int64_t>(tile_begin + tile) * kTcCodes + half * 128;   // index within the slice
+            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);                // multiple of 16
+            const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
+            if (!scan_only) {
+                // before the accumulator is needed: 16 random bits per group (two Philox calls)
+                r0 = group_head_words(group0 >> 3, grow0 + row_local, p.seed, p.offset);
+                r1 = group_head_words((group0 >> 3) + 1, grow0 + row_local, p.seed, p.offset);
+                nthr = read_nthr();
+            }
+            mbar_wait(bar_tfull + 8 * buf, (j / kTcBufs) & 1);
+            tc_fence_after();
+            if (half == 0 && (warp & 3) == 0 && lane == 0) mbar_arrive(bar_empty + 8 * (j % kTsStages));  // MMAs have read the stage
+            if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+                tmem_ld32(t_lane + ch * 32, va);
+                tmem_ld_wait32(va);
+                if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
+                    tc_fence_before();
+                    mbar_arrive(bar_tempty + 8 * buf);
+                }
+                if ((ch + 1) * 32 > valid) {   // columns beyond the slice: finite filler while scanning (it is tagged), -inf when testing
+                    const uint32_t fill = scan_only ? __float_as_uint(kTcMasked) : 0xFF800000u;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) if (ch * 32 + c >= valid) va[c] = fill;
+                }
+                const float m0 = max8(&va[0]), m1 = max8(&va[8]), m2 = max8(&va[16]), m3 = max8(&va[24]);
+                if (scan_only) {
+                    const float q0 = tag2(m0, 0u), q1 = tag2(m1, 1u), q2 = tag2(m2, 2u), q3 = tag2(m3, 3u);
+                    const float mc = fmaxf(fmaxf(q0, q1), fmaxf(q2, q3));
+                    sgrp = mc > sbest ? group0 + 4 * ch : sgrp;
+                    sbest = fmaxf(sbest, mc);
+                } else {
+                    // log2 of the chunk's four heads: the test   head < 2^(m * tl2e + thr)   is one FFMA + compare per group
+                    // (head 0 -> -inf: always a candidate)
+                    const Philox4& rr = ch < 2 ? r0 : r1;
+                    const uint32_t w0 = pick_word(rr, 2 * (ch & 1)), w1 = pick_word(rr, 2 * (ch & 1) + 1);
+                    const uint32_t h0 = w0 & 0xFFFFu, h1 = w0 >> 16, h2 = w1 & 0xFFFFu, h3 = w1 >> 16;
+                    const float c0 = fmaf(m0, tl2e, -lg2_u16(h0)), c1 = fmaf(m1, tl2e, -lg2_u16(h1));
+                    const float c2 = fmaf(m2, tl2e, -lg2_u16(h2)), c3 = fmaf(m3, tl2e, -lg2_u16(h3));
+                    const bool ev = fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)) > nthr;
+                    if (__any_sync(0xffffffffu, ev) && !(p.debug & 64)) {
+                        if (ev) {
+                            const uint32_t mk = (c0 > nthr ? 1u : 0u) | (c1 > nthr ? 2u : 0u) | (c2 > nthr ? 4u : 0u) |
+                                                (c3 > nthr ? 8u : 0u);
+                            uint32_t slot = atomicAdd(const_cast<uint32_t*>(qtail_p), __popc(mk));
+                            const uint32_t hh[4] = {h0, h1, h2, h3};
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                if (mk & (1u << g)) {
+                                    const uint32_t sl = slot & (kTsQueueSlots - 1);
+                                    uint32_t hw[4];
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i) {
+                                        const __half2 h = __floats2half2_rn(__uint_as_float(va[8 * g + 2 * i]),
+                                                                            __uint_as_float(va[8 * g + 2 * i + 1]));
+                                        hw[i] = *reinterpret_cast<const uint32_t*>(&h);
+                                    }
+                                    q_sc[sl] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                                    q_meta[sl] = make_uint2(group0 + 4 * ch + g, lane | (hh[g] << 16));
+                                    ++slot;
+                                }
+                            }
+                        }
+                        __syncwarp();
+                        // Inside a tile the ring is drained only when the next chunk could overflow it (<= 128 pushes):
+                        // while this warp expands groups its half of the accumulator is not released.  No tcgen05.ld
+                        // is in flight here, so the call may spill freely.
+                        if (ch < 3 && *qtail_p - qhead > kTsQueueSlots - 128u) {
+                            do { flush(32u); } while (*qtail_p - qhead > kTsQueueSlots - 160u);
+                            nthr = read_nthr();
+                        }
+                    }
+                }
+            }
+            if (scan_only) {
+                if (j + kTcBufs >= scout) {
+                    // last scan of this thread: expand the best approximate group -> a near-final threshold for the row
+                    const uint32_t g = sgrp + (__float_as_uint(sbest) & 3u);
+                    const Philox4 hw = group_head_words(g >> 3, grow0 + row_local, p.seed, p.offset);
+                    const uint32_t slot = atomicAdd(const_cast<uint32_t*>(qtail_p), 1u);
+                    // scores "+inf": every code of the group passes the per-code test of the expansion
+                    q_sc[slot & (kTsQueueSlots - 1)] = make_uint4(0x7C007C00u, 0x7C007C00u, 0x7C007C00u, 0x7C007C00u);
+                    q_meta[slot & (kTsQueueSlots - 1)] = make_uint2(g, lane | (head_hi16(hw, g) << 16));
+                    __syncwarp();
+                    flush(32u);
+                }
+            } else {
+                // regular drain, off the accumulator's critical path
+                const uint32_t fmin = static_cast<uint32_t>(tested < p.early_iters ? p.flush_early : p.flush_late);
+                ++tested;
+                __syncwarp();
+                for (uint32_t pending = *qtail_p - qhead; pending != 0u && pending >= fmin; pending = *qtail_p - qhead)
+                    flush(min(32u, pending));
+            }
+        }
+        __syncwarp();
+        for (uint32_t pending = *qtail_p - qhead; pending != 0u; pending = *qtail_p - qhead) flush(min(32u, pending));
+        if (p.n_events && lane == 0) atomicAdd(p.n_events, qhead);
+        // all four groups done -> publish the rows (named barrier over the 512 epilogue threads)
+        asm volatile("bar.sync 1, 512;" ::: "memory");
+        if (grp == 0) {
+            const int64_t row = row0 + row_local;
+            if (row < p.N && ntiles > 0) atomicMax(p.keys + row, s_key[row_local]);
+        }
+    }
+    // ---- teardown ------------------------------------------------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kTcEpiWarps + 1) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace b200vq
