@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 111
+#define B200VQ_VERSION 120
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -58,6 +58,11 @@ int b200vq_last_cuda_error(void);
 int b200vq_max_dim(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 uint64_t b200vq_launch_count(void);
+/* Measurement aid: a register-resident fp32 FMA loop over every SM, `iters` rounds of 8 independent
+ * chains per thread.  *out_flops_per_launch (host, nullable) = 2 * 8 * iters * threads launched; out (device, 1 float)
+ * keeps the result live.  Time it with CUDA events to get the box's fp32 FMA peak (the roofline of the exact-fp32
+ * kernels) instead of quoting the nominal 128 lanes x 2 x clock. */
+int b200vq_fma_probe(int64_t iters, float* out, double* out_flops_per_launch, b200vq_stream_t stream);
 
 /* Scratch bytes the forward/backward calls need for N tokens, D dims, K codes. */
 size_t b200vq_workspace_bytes(int64_t N, int D, int64_t K);

@@ -4,6 +4,7 @@ indices bit-exact outside a 1e-6 reference score gap; tensors/losses/grads 1e-3 
 import numpy as np
 import pytest
 import torch
+import torch.nn.functional as F
 
 import video_tokenizer_b200 as V
 from oracle import vq_oracle as O
@@ -300,3 +301,21 @@ def test_errors_are_loud():
     with pytest.raises(AssertionError):
         V.SimpleVectorQuantizer(dim=16, codebook_size=64, l2_normalized=False, stochastic=True).to(DEV)(
             torch.randn(1, 4, 16, device=DEV))
+
+
+def test_decode_is_differentiable_towards_the_codebook_when_grad_is_recorded():
+    """reference get_codebook_entry (bottleneck.py:327-341) is nn.Embedding + F.normalize: gradients reach the
+    codebook.  The kernel path builds no graph, so with grad enabled the drop-in uses the same op sequence."""
+    torch.manual_seed(31)
+    m = V.SimpleVectorQuantizer(dim=16, codebook_size=64, l2_normalized=True).to(DEV)
+    idx = torch.randint(0, 64, (2, 5), device=DEV)
+    with torch.no_grad():
+        fast = m.decode(idx)
+    slow = m.decode(idx)
+    assert slow.requires_grad and tuple(slow.shape) == (2, 5, 16)
+    assert_close(slow.detach(), fast, "decode grad path vs kernel path", tol=1e-6)
+    slow.square().sum().backward()
+    ref_w = m.embedding.weight.detach().clone().requires_grad_(True)
+    F.normalize(F.embedding(idx, ref_w), dim=-1).square().sum().backward()
+    assert torch.allclose(m.embedding.weight.grad, ref_w.grad, atol=1e-6)
+    assert tuple(m.get_codebook_entry(idx, shape=(10, 16)).shape) == (10, 16)

@@ -26,6 +26,7 @@ SIGNATURES = {
     "b200vq_last_cuda_error": (_i32, []),
     "b200vq_max_dim": (_i32, []),
     "b200vq_launch_count": (_u64, []),
+    "b200vq_fma_probe": (_i32, [_i64, _vp, _vp, _vp]),
     "b200vq_workspace_bytes": (_sz, [_i64, _i32, _i64]),
     "b200vq_prepare_codebook": (_i32, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200vq_keys_reset": (_i32, [_vp, _i64, _vp]),
@@ -100,7 +101,7 @@ def load(build_if_missing: bool = True):
             except AttributeError as e:
                 raise B200VQError(f"{path} does not export {name}") from e
             fn.restype, fn.argtypes = res, args
-        if lib.b200vq_version() < 102:
+        if lib.b200vq_version() < 120:
             raise B200VQError("libb200vq.so is older than this Python package")
         _lib = lib
         return lib

@@ -213,7 +213,16 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         return VF.usage_stats(*self.last_usage)
 
     def get_codebook_entry(self, indices, shape=None):
-        return VF.codebook_lookup(indices, self.embedding.weight, self.l2_normalized, shape)
+        """indices -> (normalised) code rows (bottleneck.py:327-341).  Inference goes through b200vq_decode; when a
+        gradient towards the codebook is being recorded the lookup is the reference's differentiable op sequence
+        (nn.Embedding + F.normalize), because the decode kernel builds no autograd graph."""
+        w = self.embedding.weight
+        if torch.is_grad_enabled() and w.requires_grad:
+            z_q = self.embedding(indices.reshape(-1))
+            if self.l2_normalized:
+                z_q = F.normalize(z_q, p=2, dim=-1)
+            return z_q.reshape(shape) if shape is not None else z_q.reshape(*indices.shape, self.dim)
+        return VF.codebook_lookup(indices, w, self.l2_normalized, shape)
 
     def decode(self, indices):
         return self.get_codebook_entry(indices)

@@ -20,6 +20,35 @@ int b200vq_last_cuda_error(void) { return g_last_cuda_error; }
 int b200vq_max_dim(void) { return kMaxDim; }
 uint64_t b200vq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+}  // extern "C"
+
+namespace {
+__global__ void __launch_bounds__(256) fma_probe_kernel(int64_t iters, float* __restrict__ out) {
+    float a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = 1.0f + 1e-3f * static_cast<float>(threadIdx.x + i);
+    const float m = 0.999999f, c = 1e-7f * static_cast<float>(blockIdx.x);
+    for (int64_t it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = fmaf(a[i], m, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += a[i];
+    if (s == 123.456f) *out = s;   // keeps the chains live; never true in practice
+}
+}  // namespace
+
+extern "C" {
+
+int b200vq_fma_probe(int64_t iters, float* out, double* out_flops_per_launch, b200vq_stream_t stream) {
+    if (iters <= 0 || !out) return B200VQ_EINVAL;
+    const unsigned blocks = static_cast<unsigned>(sm_count()) * 8u;
+    fma_probe_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(iters, out);
+    if (out_flops_per_launch) *out_flops_per_launch = 2.0 * 8.0 * static_cast<double>(iters) * blocks * 256.0;
+    return launch_check();
+}
+
 const char* b200vq_error_string(int code) {
     switch (code) {
         case B200VQ_OK: return "ok";

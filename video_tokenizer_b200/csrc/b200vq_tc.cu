@@ -18,7 +18,7 @@ template <int DD, typename T>
 int launch_ts(const TsParams& prm, dim3 grid, cudaStream_t st) {
     constexpr size_t smem = ts_smem_bytes<DD>();
     if (int rc = set_smem(tc_sample_kernel<DD, T>, smem)) return rc;
-    tc_sample_kernel<DD, T><<<grid, kTcThreads, smem, st>>>(prm);
+    tc_sample_kernel<DD, T><<<grid, kTsThreads, smem, st>>>(prm);
     return launch_check();
 }
 inline int env_int(const char* name, int fallback) {

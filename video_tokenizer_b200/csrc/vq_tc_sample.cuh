@@ -22,14 +22,22 @@
 //     tiles are tested, and the scout tiles are run again (tested) at the end.  Costs scout/ntiles more MMA
 //     work, removes most of the early candidates.
 //
-// CTA layout as in vq_tc_kernel.cuh: 128 rows x a range of 256-code tiles; warps 0-15 = four epilogue groups
-// (TMEM buffer x column half), warp 16 = bulk-copy producer, warps 17/18 = MMA issuers of even / odd iterations.
+// CTA layout: 128 rows x a range of 256-code tiles.  A tile is scored as four 64-code quarters (UMMA N = 64) and TMEM
+// holds EIGHT accumulator buffers of 64 columns: (tile parity) x (quarter).  Warps 0-15 are four epilogue groups: group
+// g (warps 4g..4g+3; warp w = rows [32*(w&3), +32)) drains quarter g of every tile, alternating between its two
+// buffers, so the quarter of the next tile is already accumulated when the group finishes the current one, and only
+// the four warps of a group are coupled through a buffer.
+// Warp 16 streams codebook tiles with cp.async.bulk through a ring of stages, warps 17 / 18 issue the MMAs of even /
+// odd tiles; a stage is handed back to the producer by a tcgen05.commit (no epilogue warp involved).
 #pragma once
 #include "vq_tc_kernel.cuh"
 
 namespace b200vq {
 
-constexpr int kTsStages = 4;          // codebook tiles in flight
+constexpr int kTsStages = 6;          // codebook tiles in flight
+constexpr int kTsThreads = 32 * (kTcEpiWarps + 3);   // 16 epilogue warps + producer + 2 MMA issuers
+constexpr int kTsBufs = 8;            // TMEM accumulator buffers (8 x 64 columns)
+constexpr int kTsPart = 64;           // codes per quarter tile (UMMA N)
 constexpr int kTsQueueSlots = 256;    // per epilogue warp (ring): <= 31 left over + <= 128 pushed per chunk
 constexpr float kTsScoreEps = 4.2e-3f;    // 2^-8 + 2^-18 (bf16 operands, unit vectors) + 2^-12 (fp16 copy in the queue) + fp32 accumulation
 
@@ -68,8 +76,10 @@ struct TsParams {
 };
 
 // ---- expand up to 32 queued groups, one per lane.  Per code of the group the bound test is repeated against the
-// row's current best; surviving codes get their exact fp32 score (the arithmetic of scores_kernel), the group's
-// Gumbels are generated, and the best perturbed value is merged into the row's key ----------------------------
+// row's current best; for the codes that survive, the group's Gumbels are generated and the APPROXIMATE perturbed
+// score is compared with the current best (most survivors of the bound die here: the largest Gumbel of a group
+// rarely sits on its best code); what is left gets its exact fp32 score (the arithmetic of scores_kernel) and is
+// merged into the row's key ----------------------------------------------------------------------------------
 template <int D>
 __device__ __noinline__ void ts_flush(const uint4* q_sc, const uint2* q_meta, uint32_t qhead, uint32_t n, uint32_t lane,
                                       uint32_t row_base, const float* s_z, unsigned long long* s_key,
@@ -81,14 +91,17 @@ __device__ __noinline__ void ts_flush(const uint4* q_sc, const uint2* q_meta, ui
         const uint2 meta = q_meta[slot];
         const uint4 sc = q_sc[slot];
         const uint32_t group = meta.x, rl = row_base + (meta.y & 31u), hi16 = meta.y >> 16;
-        const float nthr = fmaf(key_value(s_key[rl]), kLog2e, -slack19);
+        const float best_now = key_value(s_key[rl]);
+        const float nthr = fmaf(best_now, kLog2e, -slack19);
         const float lh = lg2_u16(hi16);
         const uint32_t code0 = group * 8u;
         const uint32_t w[4] = {sc.x, sc.y, sc.z, sc.w};
+        float sa[8];
         uint32_t live = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            sa[2 * i] = f.x; sa[2 * i + 1] = f.y;
             live |= fmaf(f.x, tl2e, -lh) > nthr ? (1u << (2 * i)) : 0u;
             live |= fmaf(f.y, tl2e, -lh) > nthr ? (2u << (2 * i)) : 0u;
         }
@@ -96,63 +109,86 @@ __device__ __noinline__ void ts_flush(const uint4* q_sc, const uint2* q_meta, ui
         if (live != 0u) {
             float g[8];
             group_noise(group, grow0 + rl, seed, offset, hi16, g);
-            float zn[D];
-            const float* zr = s_z + rl * ts_zstride<D>();
+            // approximate perturbed scores: only codes that can still reach the current best are worth exact scoring
+            const float margin = kTsScoreEps * t_inv;
+            uint32_t keep = 0;
 #pragma unroll
-            for (int d = 0; d < D; d += 4) {
-                const float4 t = *reinterpret_cast<const float4*>(zr + d);
-                zn[d] = t.x; zn[d + 1] = t.y; zn[d + 2] = t.z; zn[d + 3] = t.w;
-            }
-            const float* e = emb + static_cast<size_t>(code0 - k_offset) * D;
-            float bv = -INFINITY;
-            uint32_t bk = code0;
-            while (live != 0u) {                     // ascending code order: ties keep the lowest index
-                const int pos = __ffs(live) - 1;
-                live &= live - 1u;
-                float acc = 0.f;
+            for (int t = 0; t < 8; ++t) keep |= (fmaf(sa[t], t_inv, g[t]) + margin >= best_now) ? (1u << t) : 0u;
+            live &= keep;
+            if (live != 0u) {
+                float zn[D];
+                const float* zr = s_z + rl * ts_zstride<D>();
 #pragma unroll
                 for (int d = 0; d < D; d += 4) {
-                    const float4 ev = __ldg(reinterpret_cast<const float4*>(e + pos * D + d));
-                    acc = fmaf(zn[d + 0], ev.x, acc);
-                    acc = fmaf(zn[d + 1], ev.y, acc);
-                    acc = fmaf(zn[d + 2], ev.z, acc);
-                    acc = fmaf(zn[d + 3], ev.w, acc);
+                    const float4 t = *reinterpret_cast<const float4*>(zr + d);
+                    zn[d] = t.x; zn[d + 1] = t.y; zn[d + 2] = t.z; zn[d + 3] = t.w;
                 }
-                float gp = g[0];
+                const float* e = emb + static_cast<size_t>(code0 - k_offset) * D;
+                float bv = -INFINITY;
+                uint32_t bk = code0;
+                while (live != 0u) {                     // ascending code order: ties keep the lowest index
+                    const int pos = __ffs(live) - 1;
+                    live &= live - 1u;
+                    float acc = 0.f;
 #pragma unroll
-                for (int t = 1; t < 8; ++t) gp = pos == t ? g[t] : gp;
-                const float v = __fmaf_rn(acc, t_inv, gp);
-                if (v > bv) { bv = v; bk = code0 + pos; }
+                    for (int d = 0; d < D; d += 4) {
+                        const float4 ev = __ldg(reinterpret_cast<const float4*>(e + pos * D + d));
+                        acc = fmaf(zn[d + 0], ev.x, acc);
+                        acc = fmaf(zn[d + 1], ev.y, acc);
+                        acc = fmaf(zn[d + 2], ev.z, acc);
+                        acc = fmaf(zn[d + 3], ev.w, acc);
+                    }
+                    float gp = g[0];
+#pragma unroll
+                    for (int t = 1; t < 8; ++t) gp = pos == t ? g[t] : gp;
+                    const float v = __fmaf_rn(acc, t_inv, gp);
+                    if (v > bv) { bv = v; bk = code0 + pos; }
+                }
+                atomicMax(s_key + rl, make_key(bv, bk));
             }
-            atomicMax(s_key + rl, make_key(bv, bk));
         }
     }
     __syncwarp();
 }
 
+// mbarrier wait with a suspend-time hint: the thread sleeps in hardware until the phase completes or the hint
+// expires, instead of spinning through try_wait / branch (which burns issue slots the epilogue warps need)
+__device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "TS_WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra TS_WAIT_DONE;\n\t"
+        "bra TS_WAIT_LOOP;\n\t"
+        "TS_WAIT_DONE:\n\t"
+        "}" ::"r"(bar), "r"(parity), "r"(0x989680u) : "memory");
+}
+
 // =======================================================================================
-// grid = (row tiles of 128, code splits); block = kTcThreads; dynamic smem = ts_smem_bytes<D>()
+// grid = (row tiles of 128, code splits); block = kTsThreads; dynamic smem = ts_smem_bytes<D>()
 // =======================================================================================
 template <int D, typename T>
-__global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams p) {
+__global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams p) {
     constexpr int CH = ts_chunks<D>();          // K chunks per operand row (incl. zero padding)
     constexpr int P = D / 8;                    // real chunks
-    constexpr int SLABS = CH / 2;               // MMAs (K = 16) per tile
+    constexpr int SLABS = CH / 2;               // MMAs (K = 16) per quarter tile
     constexpr uint32_t A_BYTES = kTcRows * CH * 16;
     constexpr uint32_t B_BYTES = ts_stage_bytes<D>();
     constexpr uint32_t A_LBO = kTcRows * 16, B_LBO = kTcCodes * 16, SBO = 128;
     constexpr int ZS = ts_zstride<D>();
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    // 1024-byte alignment by pointer arithmetic on the shared array (keeps the shared address space: LDS / STS / ATOMS)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sA = smem;
     uint8_t* sB = sA + A_BYTES;
     float* s_z = reinterpret_cast<float*>(sB + kTsStages * B_BYTES);
     uint4* s_qsc = reinterpret_cast<uint4*>(s_z + kTcRows * ZS);                      // queued groups: 8 fp16 scores
     uint2* s_qmeta = reinterpret_cast<uint2*>(s_qsc + kTcEpiWarps * kTsQueueSlots);     // (group, lane | head << 16)
     unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_qmeta + kTcEpiWarps * kTsQueueSlots);
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_key + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTsStages + 2 * kTcBufs);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_key + kTcRows);  // full[S], empty[S], tfull[8], tempty[8]
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTsStages + 2 * kTsBufs);
     uint32_t* s_qtail = s_tmem + 4;   // (kTcEpiWarps) queue tails
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -165,7 +201,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
     const uint32_t first_code = static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes;
 
     const uint32_t bar_full = smem_u32(s_bar), bar_empty = bar_full + 8 * kTsStages;
-    const uint32_t bar_tfull = bar_empty + 8 * kTsStages, bar_tempty = bar_tfull + 8 * kTcBufs;
+    const uint32_t bar_tfull = bar_empty + 8 * kTsStages, bar_tempty = bar_tfull + 8 * kTsBufs;
 
     // ---- prologue ---------------------------------------------------------------------------------
     if (threadIdx.x < kTcRows) {
@@ -199,7 +235,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
     } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTsStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-            for (int b = 0; b < kTcBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 256); }
+            for (int b = 0; b < kTsBufs; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 4); }
             fence_barrier_init();
         }
     } else if (warp == kTcEpiWarps + 1) {
@@ -208,7 +244,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
     if constexpr (CH > P) {
         // zero K-padding chunks of every codebook stage (the bulk copies only write chunks [0, P))
         constexpr int PAD16 = (CH - P) * kTcCodes;   // 16-byte words per stage
-        for (int i = threadIdx.x; i < kTsStages * PAD16; i += kTcThreads) {
+        for (int i = threadIdx.x; i < kTsStages * PAD16; i += kTsThreads) {
             const int s = i / PAD16, o = i % PAD16;
             *reinterpret_cast<uint4*>(sB + s * B_BYTES + P * B_LBO + o * 16) = make_uint4(0u, 0u, 0u, 0u);
         }
@@ -226,36 +262,41 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
             for (int j = 0; j < iters; ++j) {
                 const int s = j % kTsStages;
                 const int tile = j < ntiles ? j : j - ntiles;
-                mbar_wait(bar_empty + 8 * s, ((j / kTsStages) & 1) ^ 1);
+                mbar_wait_hint(bar_empty + 8 * s, ((j / kTsStages) & 1) ^ 1);
                 mbar_expect_tx(bar_full + 8 * s, ts_copy_bytes<D>());
                 bulk_g2s(smem_u32(sB + s * B_BYTES), src + static_cast<size_t>(tile) * tc_tile_bytes(D), ts_copy_bytes<D>(),
                          bar_full + 8 * s);
             }
         }
-    } else if (warp >= kTcEpiWarps + 1) {
-        // ===== MMA issuers: warp 17 issues the iterations of buffer 0, warp 18 those of buffer 1 ===============
+    } else if (warp > kTcEpiWarps) {
+        // ===== MMA issuers: warp 17 issues even iterations (buffers 0-3), warp 18 odd ones (buffers 4-7) ============
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTcCodes);
-            const int buf = warp - (kTcEpiWarps + 1);
+            constexpr uint32_t idesc = umma_idesc_bf16(kTcRows, kTsPart);
             const uint32_t a0 = smem_u32(sA);
-            for (int j = buf; j < iters; j += kTcBufs) {
+            const int par = warp - (kTcEpiWarps + 1);
+            for (int j = par; j < iters; j += 2) {
                 const int s = j % kTsStages;
-                mbar_wait(bar_tempty + 8 * buf, ((j / kTcBufs) & 1) ^ 1);
-                mbar_wait(bar_full + 8 * s, (j / kTsStages) & 1);
-                tc_fence_after();
-                const uint32_t b0 = smem_u32(sB + s * B_BYTES);
+                mbar_wait_hint(bar_full + 8 * s, (j / kTsStages) & 1);
 #pragma unroll
-                for (int k = 0; k < SLABS; ++k) {
-                    if (p.debug & 1) break;
-                    umma_bf16(tmem_base + buf * kTcCodes, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
-                              umma_desc(b0 + k * 2 * B_LBO, B_LBO, SBO), idesc, k > 0);
+                for (int part = 0; part < 4; ++part) {
+                    const int buf = par * 4 + part;
+                    mbar_wait_hint(bar_tempty + 8 * buf, ((j >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t b0 = smem_u32(sB + s * B_BYTES) + part * (kTsPart * 16);
+#pragma unroll
+                    for (int k = 0; k < SLABS; ++k) {
+                        if (p.debug & 1) break;
+                        umma_bf16(tmem_base + buf * kTsPart, umma_desc(a0 + k * 2 * A_LBO, A_LBO, SBO),
+                                  umma_desc(b0 + k * 2 * B_LBO, B_LBO, SBO), idesc, k > 0);
+                    }
+                    umma_commit(bar_tfull + 8 * buf);
                 }
-                umma_commit(bar_tfull + 8 * buf);   // the epilogue group that sees it also frees the codebook stage
+                umma_commit(bar_empty + 8 * s);   // all four quarters have read the stage once this fires
             }
         }
     } else {
-        // ===== epilogue groups: group g = warps 4g..4g+3, columns [128*(g&1), +128) of buffer g>>1 ==========
-        const int grp = warp >> 2, buf = grp >> 1, half = grp & 1;
+        // ===== epilogue: group g = warps 4g..4g+3 drains quarter g of every tile; warp w = rows [32*(w&3), +32) =======
+        const uint32_t grp = warp >> 2;
         const uint32_t row_base = 32u * (warp & 3);
         const uint32_t row_local = row_base + lane;
         uint4* q_sc = s_qsc + warp * kTsQueueSlots;
@@ -263,9 +304,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
         volatile uint32_t* qtail_p = s_qtail + warp;
         uint32_t qhead = 0;   // warp-uniform
         const uint32_t grow0 = static_cast<uint32_t>(p.row_offset + row0);
+        const uint32_t grow = grow0 + row_local;
         const uint32_t k_off32 = static_cast<uint32_t>(p.k_offset);
         const uint32_t k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
-        const uint32_t t_lane = tmem_base + (row_base << 16) + buf * kTcCodes + half * 128;
+        const uint32_t t_lane = tmem_base + (row_base << 16) + grp * kTsPart;
         const float tl2e = p.t_inv * kLog2e;
         // candidate iff  m * tl2e - log2(head)  >  vstar * log2(e) - (19 + slack):   slack covers the score error
         // (kTsScoreEps / T in log2 units) and the lg2 / FFMA rounding of the test itself
@@ -277,51 +319,58 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
             qhead += n;
         };
         float nthr = -INFINITY;      // "everything can matter" until the row has a key
-        float sbest = -INFINITY;     // scout: best tagged group maximum, and the first group of its 32-column chunk
-        uint32_t sgrp = first_code >> 3;
+        float sbest = -INFINITY;     // scan: best tagged score (position within its 32-column chunk in the low 5 bits)
+        uint32_t scode = first_code; // ... and the first code of that chunk
         uint32_t va[32];
-        Philox4 r0{}, r1{};          // 16 random bits per group: the heads of this thread's 16 groups of the tile
         int tested = 0;
-        for (int j = buf; j < iters; j += kTcBufs) {
-            const bool scan_only = j < scout;
-            const int tile = j < ntiles ? j : j - ntiles;
-            const int64_t code0 = static_cast<int64_t>(tile_begin + tile) * kTcCodes + half * 128;   // index within the slice
-            const uint32_t group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);                // multiple of 16
-            const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
+        const uint32_t uiters = static_cast<uint32_t>(iters), uscout = static_cast<uint32_t>(scout);
+        for (uint32_t j = 0; j < uiters; ++j) {
+            const uint32_t buf = (j & 1u) * 4u + grp;
+            const bool scan_only = j < uscout;
+            const uint32_t tile = j < static_cast<uint32_t>(ntiles) ? j : j - ntiles;
+            const uint32_t code0 = first_code + tile * kTcCodes + grp * kTsPart;          // global code id of column 0
+            const uint32_t group0 = code0 >> 3;                                          // multiple of 8
+            const int valid = static_cast<int>(min(static_cast<uint32_t>(kTsPart), k_end_global > code0 ? k_end_global - code0 : 0u));
+            Philox4 r0{};
             if (!scan_only) {
-                // before the accumulator is needed: 16 random bits per group (two Philox calls)
-                r0 = group_head_words(group0 >> 3, grow0 + row_local, p.seed, p.offset);
-                r1 = group_head_words((group0 >> 3) + 1, grow0 + row_local, p.seed, p.offset);
+                // before the accumulator is needed: 16 random bits for each of the 8 groups (one Philox call)
+                r0 = group_head_words(group0 >> 3, grow, p.seed, p.offset);
                 nthr = read_nthr();
             }
-            mbar_wait(bar_tfull + 8 * buf, (j / kTcBufs) & 1);
+            mbar_wait_hint(bar_tfull + 8 * buf, (j >> 1) & 1);
             tc_fence_after();
-            if (half == 0 && (warp & 3) == 0 && lane == 0) mbar_arrive(bar_empty + 8 * (j % kTsStages));  // MMAs have read the stage
-            if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
+            if (p.debug & 2) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                continue;
+            }
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-                tmem_ld32(t_lane + ch * 32, va);
+            for (int ch = 0; ch < 2; ++ch) {
+                tmem_ld32(t_lane + (j & 1u) * 256u + ch * 32, va);
                 tmem_ld_wait32(va);
-                if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
+                if (ch == 1) {   // the warp's rows of the buffer are in registers: hand them back to the MMA warp
                     tc_fence_before();
-                    mbar_arrive(bar_tempty + 8 * buf);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
                 }
                 if ((ch + 1) * 32 > valid) {   // columns beyond the slice: finite filler while scanning (it is tagged), -inf when testing
                     const uint32_t fill = scan_only ? __float_as_uint(kTcMasked) : 0xFF800000u;
 #pragma unroll
                     for (int c = 0; c < 32; ++c) if (ch * 32 + c >= valid) va[c] = fill;
                 }
-                const float m0 = max8(&va[0]), m1 = max8(&va[8]), m2 = max8(&va[16]), m3 = max8(&va[24]);
                 if (scan_only) {
-                    const float q0 = tag2(m0, 0u), q1 = tag2(m1, 1u), q2 = tag2(m2, 2u), q3 = tag2(m3, 3u);
-                    const float mc = fmaxf(fmaxf(q0, q1), fmaxf(q2, q3));
-                    sgrp = mc > sbest ? group0 + 4 * ch : sgrp;
+                    // best single code of the chunk: every score carries its column in its 5 low mantissa bits
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) va[c] = (va[c] & ~31u) | static_cast<uint32_t>(c);
+                    const float mc = fmaxf(fmaxf(max8(&va[0]), max8(&va[8])), fmaxf(max8(&va[16]), max8(&va[24])));
+                    scode = mc > sbest ? code0 + 32u * ch : scode;
                     sbest = fmaxf(sbest, mc);
                 } else {
+                    const float m0 = max8(&va[0]), m1 = max8(&va[8]), m2 = max8(&va[16]), m3 = max8(&va[24]);
                     // log2 of the chunk's four heads: the test   head < 2^(m * tl2e + thr)   is one FFMA + compare per group
                     // (head 0 -> -inf: always a candidate)
-                    const Philox4& rr = ch < 2 ? r0 : r1;
-                    const uint32_t w0 = pick_word(rr, 2 * (ch & 1)), w1 = pick_word(rr, 2 * (ch & 1) + 1);
+                    const uint32_t w0 = pick_word(r0, 2 * ch), w1 = pick_word(r0, 2 * ch + 1);
                     const uint32_t h0 = w0 & 0xFFFFu, h1 = w0 >> 16, h2 = w1 & 0xFFFFu, h3 = w1 >> 16;
                     const float c0 = fmaf(m0, tl2e, -lg2_u16(h0)), c1 = fmaf(m1, tl2e, -lg2_u16(h1));
                     const float c2 = fmaf(m2, tl2e, -lg2_u16(h2)), c3 = fmaf(m3, tl2e, -lg2_u16(h3));
@@ -330,8 +379,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
                         if (ev) {
                             const uint32_t mk = (c0 > nthr ? 1u : 0u) | (c1 > nthr ? 2u : 0u) | (c2 > nthr ? 4u : 0u) |
                                                 (c3 > nthr ? 8u : 0u);
-                            uint32_t slot = atomicAdd(const_cast<uint32_t*>(qtail_p), __popc(mk));
-                            const uint32_t hh[4] = {h0, h1, h2, h3};
+                            uint32_t slot = atomicAdd(s_qtail + warp, __popc(mk));
+                            const uint32_t hd[4] = {h0, h1, h2, h3};
 #pragma unroll
                             for (int g = 0; g < 4; ++g) {
                                 if (mk & (1u << g)) {
@@ -344,16 +393,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
                                         hw[i] = *reinterpret_cast<const uint32_t*>(&h);
                                     }
                                     q_sc[sl] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                                    q_meta[sl] = make_uint2(group0 + 4 * ch + g, lane | (hh[g] << 16));
+                                    q_meta[sl] = make_uint2(group0 + 4 * ch + g, lane | (hd[g] << 16));
                                     ++slot;
                                 }
                             }
                         }
                         __syncwarp();
-                        // Inside a tile the ring is drained only when the next chunk could overflow it (<= 128 pushes):
-                        // while this warp expands groups its half of the accumulator is not released.  No tcgen05.ld
-                        // is in flight here, so the call may spill freely.
-                        if (ch < 3 && *qtail_p - qhead > kTsQueueSlots - 128u) {
+                        // Inside a quarter tile the ring is drained only when the next chunk could overflow it (<= 128
+                        // pushes): while this warp expands groups its rows of the accumulator are not released.  No
+                        // tcgen05.ld is in flight here, so the call may spill freely.
+                        if (ch == 0 && *qtail_p - qhead > kTsQueueSlots - 128u) {
                             do { flush(32u); } while (*qtail_p - qhead > kTsQueueSlots - 160u);
                             nthr = read_nthr();
                         }
@@ -361,14 +410,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_sample_kernel(const TsParams
                 }
             }
             if (scan_only) {
-                if (j + kTcBufs >= scout) {
-                    // last scan of this thread: expand the best approximate group -> a near-final threshold for the row
-                    const uint32_t g = sgrp + (__float_as_uint(sbest) & 3u);
-                    const Philox4 hw = group_head_words(g >> 3, grow0 + row_local, p.seed, p.offset);
-                    const uint32_t slot = atomicAdd(const_cast<uint32_t*>(qtail_p), 1u);
-                    // scores "+inf": every code of the group passes the per-code test of the expansion
-                    q_sc[slot & (kTsQueueSlots - 1)] = make_uint4(0x7C007C00u, 0x7C007C00u, 0x7C007C00u, 0x7C007C00u);
-                    q_meta[slot & (kTsQueueSlots - 1)] = make_uint2(g, lane | (head_hi16(hw, g) << 16));
+                if (j + 1 == uscout) {
+                    // last scan: expand the row's best approximate code of this group's columns -> a
+                    // near-final threshold for the row
+                    const uint32_t code = scode + (__float_as_uint(sbest) & 31u), g = code >> 3, pos = code & 7u;
+                    const Philox4 hw = group_head_words(g >> 3, grow, p.seed, p.offset);
+                    const uint32_t slot = atomicAdd(s_qtail + warp, 1u) & (kTsQueueSlots - 1);
+                    // scores: +inf for the chosen code (passes every test of the expansion), -inf for the other seven
+                    uint32_t hw4[4] = {0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (static_cast<int>(pos >> 1) == i) hw4[i] = (pos & 1u) ? 0x7C00FC00u : 0xFC007C00u;
+                    q_sc[slot] = make_uint4(hw4[0], hw4[1], hw4[2], hw4[3]);
+                    q_meta[slot] = make_uint2(g, lane | (head_hi16(hw, g) << 16));
                     __syncwarp();
                     flush(32u);
                 }
