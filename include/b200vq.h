@@ -299,6 +299,10 @@ int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t 
  *   backward outputs (each nullable = not needed): grad_x (N,C; ldgx), grad_w_in (D,C), grad_b_in (D),
  *            grad_weight (K,D), grad_w_out (C,D), grad_b_out (C)
  *   workspace >= b200vq_bottleneck_workspace_bytes(N,C,D,K), 16-byte aligned, same buffer both ways
+ *   philox_dev (forward, nullable): DEVICE {seed, offset} (2 x uint64).  When given (stochastic mode on the
+ *            tensor-core path only) it overrides seed / offset and the library adds 4 to the offset on the device
+ *            after the draw (a one-thread kernel) -- the host-side generator advance of functional.philox_state, moved to the GPU so that a
+ *            captured CUDA graph draws fresh noise on every replay (SURVEY.md 8b "Threading").
  */
 size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K);
 int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
@@ -307,7 +311,7 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
                               float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
                               float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
-                              b200vq_stream_t stream);
+                              uint64_t* philox_dev, b200vq_stream_t stream);
 int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
                                const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
                                int64_t N, int C, const float* w_in, const float* w_out, const float* emb,

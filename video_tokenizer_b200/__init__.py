@@ -8,6 +8,7 @@ GPU; calling it does (there is no CPU fallback).
 """
 from . import _lib, registry
 from .bottleneck import AbstractRegularizer, Bottleneck, SimpleVectorQuantizer, entropy_loss
+from .graphed import GraphedBottleneckStep
 from .functional import codebook_lookup, prepare_codebook, usage_stats, vq_quantize
 from .registry import install, make, register
 from .simvq import SimVQ
@@ -15,7 +16,7 @@ from .sq import VectorQuantizer
 
 __all__ = ["Bottleneck", "SimpleVectorQuantizer", "VectorQuantizer", "SimVQ", "AbstractRegularizer", "entropy_loss", "vq_quantize",
            "codebook_lookup", "prepare_codebook", "usage_stats", "install", "make", "register", "registry",
-           "load_library"]
+           "load_library", "GraphedBottleneckStep"]
 __version__ = "0.1.0"
 
 

@@ -100,6 +100,7 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         # B200 extras (accepted through **kwargs by the reference signature too)
         self.return_usage = bool(kwargs.get("return_usage", False))
         self.last_usage = None  # (hist_first, hist_batch) int32 (K,) of the last forward
+        self.philox_dev = None  # int64[2] device {seed, offset} when the RNG state lives on the GPU (CUDA graphs)
         if dim > 1024:
             raise ValueError(f"bottleneck dim {dim} > 1024 is not supported by the B200 quantizer")
 
@@ -118,13 +119,33 @@ class SimpleVectorQuantizer(AbstractRegularizer):
             return F.normalize(w, p=2, dim=-1)
         return w
 
+    def enable_device_rng(self, device=None):
+        """Move the sampler's Philox (seed, offset) to the GPU: the kernels read it there and advance the offset
+        themselves, so a captured CUDA graph draws fresh noise on every replay.  The state starts from the torch
+        CUDA generator (and consumes nothing from it afterwards); call again to re-synchronise with the generator.
+        Only the one-call `Bottleneck` path on the tensor-core sampler reads it."""
+        dev = torch.device(device) if device is not None else self.embedding.weight.device
+        gen = torch.cuda.default_generators[dev.index if dev.index is not None else torch.cuda.current_device()]
+        seed = gen.initial_seed() & 0xFFFFFFFFFFFFFFFF
+        state = torch.tensor([seed if seed < 2 ** 63 else seed - 2 ** 64, gen.get_offset()], dtype=torch.int64)
+        if self.philox_dev is None or self.philox_dev.device != dev:
+            self.philox_dev = state.to(dev)
+        else:
+            self.philox_dev.copy_(state)
+        return self.philox_dev
+
+    def disable_device_rng(self):
+        self.philox_dev = None
+
     def _mode(self):
         if self.stochastic:
             return _lib.MODE_ARGMAX_COS if (self.eval_deterministic and not self.training) else _lib.MODE_SAMPLE
         return _lib.MODE_ARGMIN_DIST
 
-    def _step_config(self, device):
-        """(mode, 1/T, philox seed, philox offset) of this call, after the reference's checks."""
+    def _step_config(self, device, device_rng_ok=False):
+        """(mode, 1/T, philox seed, philox offset) of this call, after the reference's checks.  With
+        `device_rng_ok` (the one-call Bottleneck path) a GPU-resident state (`enable_device_rng`) replaces the
+        host-side draw from the torch generator; every other path keeps using the generator."""
         if self.stochastic:
             assert self.l2_normalized, "Stochastic sampling requires l2 normalization"
             if self.entropy_loss_weight > 0:
@@ -132,7 +153,7 @@ class SimpleVectorQuantizer(AbstractRegularizer):
         mode = self._mode()
         t_inv = float(self.stochastic_temperature_inv) if self.stochastic else 1.0
         seed = offset = 0
-        if mode == _lib.MODE_SAMPLE:
+        if mode == _lib.MODE_SAMPLE and not (device_rng_ok and self.philox_dev is not None):
             seed, offset = VF.philox_state(device)
         return mode, t_inv, seed, offset
 
@@ -329,11 +350,12 @@ class Bottleneck(nn.Module):
                 and self.project_dim == self.bottleneck_dim and len(x.shape) == 3 and self.in_linear.bias is not None
                 and VF.bottleneck_supported(x, self.in_linear.weight, reg.embedding.weight, self.out_linear.weight)):
             # one host call per direction: in_linear -> quantizer -> out_linear (+ usage statistics)
-            mode, t_inv, seed, offset = reg._step_config(x.device)
+            mode, t_inv, seed, offset = reg._step_config(x.device, device_rng_ok=True)
             x_hat, projected_z, znorm, emb, ste, idx, lq, lc, lcb, hists, usage, norms = VF.bottleneck_step(
                 x, self.in_linear.weight, self.in_linear.bias, reg.embedding.weight, self.out_linear.weight,
                 self.out_linear.bias, mode=mode, l2norm=reg.l2_normalized, t_inv=t_inv, beta=reg.beta,
-                w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset)
+                w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset,
+                philox_dev=reg.philox_dev if mode == _lib.MODE_SAMPLE else None)
             regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, (lq, lc, lcb), hists[0], hists[1], usage)
             bottleneck_rep = regularized_output.pop("bottleneck_rep")
             input_norm_first, input_norm_last = norms[0], norms[1]

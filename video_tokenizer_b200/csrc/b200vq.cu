@@ -180,34 +180,67 @@ int b200vq_finish(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, i
     return launch_check();
 }
 
+}  // extern "C"
+
+namespace {
+// b200vq_forward with a device-resident Philox state (nullable `philox_dev`), as the whole-Bottleneck call passes it
+int forward_impl(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb, const float* e2,
+                 const void* image, int64_t K, int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                 unsigned long long* philox_dev, int64_t n_first, float beta, float w_cb, float* znorm_out, float* ste_out,
+                 int64_t* idx_out, float* zlen_out, int32_t* hist, int32_t* hist_first, float* losses, void* workspace,
+                 size_t workspace_bytes, cudaStream_t st) {
+    if (N <= 0 || K <= 0) return B200VQ_EINVAL;
+    if (!workspace || workspace_bytes < b200vq_workspace_bytes(N, D, K)) return B200VQ_EWORKSPACE;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
+    uint64_t* keys = static_cast<uint64_t*>(workspace);
+    double* scratch = reinterpret_cast<double*>(static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8));
+    const bool tc = image && b200vq_tc_supported(D, l2norm, mode);
+    int rc;
+    // histograms: one fill when the two are adjacent (the (2, K) tensor of the one-call path)
+    if (hist && hist_first && hist_first == hist + K) {
+        if ((rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 8, st)))) return rc;
+    } else {
+        if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
+        if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
+    }
+    if (tc && mode == B200VQ_MODE_SAMPLE) {
+        // keys + sums are zeroed; the deterministic modes' scratch is not needed
+        if ((rc = cuda_check(cudaMemsetAsync(workspace, 0, align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double)), st))))
+            return rc;
+        rc = host::launch_tc_sample(z, z_dtype, z_row_stride, N, D, image, emb, K, 0, l2norm, t_inv, seed, offset, philox_dev, 0,
+                                    keys, nullptr, st);
+        if (rc) return rc;
+        return b200vq_finish(z, z_dtype, z_row_stride, N, D, emb, K, keys, nullptr, l2norm, n_first, znorm_out, ste_out, idx_out,
+                             zlen_out, hist, hist_first, scratch, 1, N, beta, w_cb, losses, st);
+    }
+    if (philox_dev && mode == B200VQ_MODE_SAMPLE) return B200VQ_EINVAL;   // only the tensor-core sampler reads a device-side state
+    if ((rc = cuda_check(cudaMemsetAsync(workspace, 0, b200vq_workspace_bytes(N, D, K), st)))) return rc;
+    if (tc) {
+        char* base = static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double));
+        unsigned int* n_resolved = reinterpret_cast<unsigned int*>(base);
+        float* second = reinterpret_cast<float*>(base + align_up(sizeof(unsigned int)));
+        rc = b200vq_scores_tc(z, z_dtype, z_row_stride, N, D, image, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
+                              keys, second, n_resolved, st);
+    } else {
+        rc = b200vq_scores_partial(z, z_dtype, z_row_stride, N, D, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
+                                   keys, st);
+    }
+    if (rc) return rc;
+    return b200vq_finish(z, z_dtype, z_row_stride, N, D, emb, K, keys, nullptr, l2norm, n_first, znorm_out, ste_out, idx_out,
+                         zlen_out, hist, hist_first, scratch, 1, N, beta, w_cb, losses, st);
+}
+}  // namespace
+
+extern "C" {
+
 int b200vq_forward(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const float* emb,
                    const float* e2, const void* image, int64_t K, int mode, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
                    int64_t n_first, float beta, float w_cb, float* znorm_out, float* ste_out, int64_t* idx_out,
                    float* zlen_out, int32_t* hist, int32_t* hist_first, float* losses, void* workspace,
                    size_t workspace_bytes, b200vq_stream_t stream) {
-    if (N <= 0 || K <= 0) return B200VQ_EINVAL;
-    if (!workspace || workspace_bytes < b200vq_workspace_bytes(N, D, K)) return B200VQ_EWORKSPACE;
-    if (reinterpret_cast<uintptr_t>(workspace) & 15) return B200VQ_EALIGN;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    uint64_t* keys = static_cast<uint64_t*>(workspace);
-    double* scratch = reinterpret_cast<double*>(static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8));
-    int rc = cuda_check(cudaMemsetAsync(workspace, 0, b200vq_workspace_bytes(N, D, K), st));
-    if (rc) return rc;
-    if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
-    if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
-    if (image && b200vq_tc_supported(D, l2norm, mode)) {
-        char* base = static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double));
-        unsigned int* n_resolved = reinterpret_cast<unsigned int*>(base);
-        float* second = reinterpret_cast<float*>(base + align_up(sizeof(unsigned int)));
-        rc = b200vq_scores_tc(z, z_dtype, z_row_stride, N, D, image, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
-                              keys, second, n_resolved, stream);
-    } else {
-        rc = b200vq_scores_partial(z, z_dtype, z_row_stride, N, D, emb, e2, K, 0, mode, l2norm, t_inv, seed, offset, 0,
-                                   keys, stream);
-    }
-    if (rc) return rc;
-    return b200vq_finish(z, z_dtype, z_row_stride, N, D, emb, K, keys, nullptr, l2norm, n_first, znorm_out, ste_out, idx_out,
-                         zlen_out, hist, hist_first, scratch, 1, N, beta, w_cb, losses, stream);
+    return forward_impl(z, z_dtype, z_row_stride, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset, nullptr, n_first,
+                        beta, w_cb, znorm_out, ste_out, idx_out, zlen_out, hist, hist_first, losses, workspace, workspace_bytes,
+                        static_cast<cudaStream_t>(stream));
 }
 
 int b200vq_backward(const float* g_ste, const float* g_znorm, const float* g_loss, const float* znorm,
@@ -347,7 +380,7 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
                               float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
                               float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
-                              b200vq_stream_t stream) {
+                              uint64_t* philox_dev, b200vq_stream_t stream) {
     if (N <= 0 || K <= 0 || !valid_mode(mode)) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !weight || !w_out || !z || !emb || !wnorm || !znorm || !ste || !idx || !zlen || !hist || !hist_first ||
@@ -373,8 +406,9 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
         image = ws + l.image;
         if ((rc = b200vq_prepare_codebook_tc(emb, K, D, image, stream))) return rc;
     }
-    rc = b200vq_forward(z, B200VQ_DT_F32, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset, n_first, beta, w_cb,
-                        znorm, ste, idx, zlen, hist, hist_first, losses, ws + l.vq, b200vq_workspace_bytes(N, D, K), stream);
+    rc = forward_impl(z, B200VQ_DT_F32, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset,
+                      reinterpret_cast<unsigned long long*>(philox_dev), n_first, beta, w_cb, znorm, ste, idx, zlen, hist,
+                      hist_first, losses, ws + l.vq, b200vq_workspace_bytes(N, D, K), st);
     if (rc) return rc;
     if (usage4 && (rc = b200vq_usage_stats(hist_first, hist, K, usage4, stream))) return rc;
     return b200vq_linear_out(ste, N, D, w_out, 0, b_out, C, out, ldo, stream);

@@ -64,6 +64,13 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
 int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
                        float* colsum, float* partial, cudaStream_t st);
 
+// ---- b200vq_tc.cu -> b200vq.cu: the tensor-core sampler ---------------------------------------------------------
+// philox_dev: nullable device {seed, offset}; when given it overrides seed / offset and the offset is advanced by 4 on
+// the device (a one-thread kernel behind the sampler), the GPU-side twin of functional.philox_state.
+int launch_tc_sample(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const void* image, const float* emb,
+                     int64_t K, int64_t k_offset, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                     unsigned long long* philox_dev, int64_t row_offset, uint64_t* keys, unsigned int* n_events, cudaStream_t st);
+
 }  // namespace host
 }  // namespace b200vq
 

@@ -27,6 +27,83 @@ inline int env_int(const char* name, int fallback) {
 }
 }  // namespace
 
+namespace {
+__global__ void philox_advance_kernel(unsigned long long* st, unsigned long long inc) { st[1] += inc; }
+
+// code splits: fill the SMs, keep the last wave full, keep >= 4 tiles per CTA when possible
+inline int tc_code_splits(int64_t row_tiles, int total_tiles) {
+    const int sms = sm_count();
+    int best_splits = 1;
+    double best_cost = 1e30;
+    for (int sp = 1; sp <= total_tiles; sp *= 2) {
+        const int per = (total_tiles + sp - 1) / sp;
+        if (sp > 1 && per < 4) break;
+        const int real = (total_tiles + per - 1) / per;
+        const double ctas = static_cast<double>(row_tiles) * real;
+        // measured (tools/tc_probe.py): a CTA costs ~6.5 tiles of prologue/teardown on top of its tiles,
+        // and CTAs of later waves start as soon as an SM frees up
+        const double waves = ctas <= sms ? 1.0 : ctas / sms;
+        const double cost = waves * (per + 6.5);
+        if (cost < best_cost) { best_cost = cost; best_splits = sp; }
+    }
+    if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
+        const int v = std::atoi(env);
+        if (v >= 1 && v <= total_tiles) best_splits = v;
+    }
+    return best_splits;
+}
+}  // namespace
+
+namespace b200vq {
+namespace host {
+int launch_tc_sample(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, int D, const void* image, const float* emb,
+                     int64_t K, int64_t k_offset, int l2norm, float t_inv, uint64_t seed, uint64_t offset,
+                     unsigned long long* philox_dev, int64_t row_offset, uint64_t* keys, unsigned int* n_events, cudaStream_t st) {
+    if (N < 0 || K <= 0 || k_offset < 0 || row_offset < 0 || !valid_dtype(z_dtype)) return B200VQ_EINVAL;
+    if (!tc_dim_ok(D)) return B200VQ_EDIM;
+    if (!l2norm) return B200VQ_EINVAL;
+    if (N == 0) return B200VQ_OK;
+    if (!z || !image || !emb || z_row_stride < D) return B200VQ_EINVAL;
+    if (k_offset & (kTcCodes - 1)) return B200VQ_EALIGN;
+    if (k_offset + K > 0xFFFFFFFFll || row_offset + N > 0xFFFFFFFFll) return B200VQ_EINVAL;
+    const int64_t row_tiles = (N + kTcRows - 1) / kTcRows;
+    const int total_tiles = static_cast<int>((K + kTcCodes - 1) / kTcCodes);
+    const int want = tc_code_splits(row_tiles, total_tiles);
+    const int per = (total_tiles + want - 1) / want;
+    const int splits = (total_tiles + per - 1) / per;
+    if (!keys) return B200VQ_EINVAL;
+    // second-generation sampler (vq_tc_sample.cuh): bf16 filter + exact expansion of the candidates
+    TsParams ts{};
+    ts.z = z; ts.z_row_stride = z_row_stride; ts.N = N; ts.image = static_cast<const uint8_t*>(image); ts.emb = emb;
+    ts.K = K; ts.k_offset = k_offset; ts.tiles_per_split = per; ts.l2norm = l2norm; ts.t_inv = t_inv;
+    ts.seed = seed; ts.offset = offset; ts.row_offset = row_offset; ts.philox_dev = philox_dev;
+    ts.keys = reinterpret_cast<unsigned long long*>(keys); ts.n_events = n_events;
+    ts.debug = env_int("B200VQ_TC_DEBUG", 0);
+    // warm start: scan the first eighth of the CTA's tiles for the row's best code before testing
+    ts.scout_tiles = std::min(per, std::max(0, env_int("B200VQ_TS_SCOUT", per >= 16 ? per / 8 : (per >= 8 ? 1 : 0))));
+    ts.flush_early = std::max(1, env_int("B200VQ_TS_FLUSH_EARLY", 8));
+    ts.flush_late = std::max(1, env_int("B200VQ_TS_FLUSH_LATE", 32));
+    ts.early_iters = env_int("B200VQ_TS_EARLY_ITERS", 2);
+    dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+    int rc = B200VQ_OK;
+    B200VQ_DISPATCH_DTYPE(z_dtype, T, {
+        switch (D) {
+            case 8: rc = launch_ts<8, T>(ts, grid, st); break;
+            case 16: rc = launch_ts<16, T>(ts, grid, st); break;
+            case 24: rc = launch_ts<24, T>(ts, grid, st); break;
+            default: rc = launch_ts<32, T>(ts, grid, st); break;
+        }
+    });
+    if (rc) return rc;
+    if (philox_dev) {
+        philox_advance_kernel<<<1, 1, 0, st>>>(philox_dev, 4ull);
+        rc = launch_check();
+    }
+    return rc;
+}
+}  // namespace host
+}  // namespace b200vq
+
 extern "C" {
 
 // ---- tensor-core path --------------------------------------------------------------------------
@@ -80,25 +157,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int64_t row_tiles = (N + kTcRows - 1) / kTcRows;
     const int total_tiles = static_cast<int>((K + kTcCodes - 1) / kTcCodes);
-    // code splits: fill the SMs, keep the last wave full, keep >= 4 tiles per CTA when possible
-    const int sms = sm_count();
-    int best_splits = 1;
-    double best_cost = 1e30;
-    for (int sp = 1; sp <= total_tiles; sp *= 2) {
-        const int per = (total_tiles + sp - 1) / sp;
-        if (sp > 1 && per < 4) break;
-        const int real = (total_tiles + per - 1) / per;
-        const double ctas = static_cast<double>(row_tiles) * real;
-        // measured (tools/tc_probe.py): a CTA costs ~6.5 tiles of prologue/teardown on top of its tiles,
-        // and CTAs of later waves start as soon as an SM frees up
-        const double waves = ctas <= sms ? 1.0 : ctas / sms;
-        const double cost = waves * (per + 6.5);
-        if (cost < best_cost) { best_cost = cost; best_splits = sp; }
-    }
-    if (const char* env = std::getenv("B200VQ_TC_SPLITS")) {  // tuning aid
-        const int v = std::atoi(env);
-        if (v >= 1 && v <= total_tiles) best_splits = v;
-    }
+    const int best_splits = tc_code_splits(row_tiles, total_tiles);
     const int per = (total_tiles + best_splits - 1) / best_splits;
     const int splits = (total_tiles + per - 1) / per;
     TcParams prm;
@@ -111,38 +170,22 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     if (const char* env = std::getenv("B200VQ_TC_DEBUG")) prm.debug = std::atoi(env);
     dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
     int rc = B200VQ_OK;
-    static const bool old_sampler = std::getenv("B200VQ_TS_OLD") != nullptr;   // tuning aid: the first-generation sampler
-    if (mode == B200VQ_MODE_SAMPLE && !old_sampler) {
-        // second-generation sampler (vq_tc_sample.cuh): bf16 filter + exact expansion of the candidates
-        TsParams ts;
-        ts.z = z; ts.z_row_stride = z_row_stride; ts.N = N; ts.image = static_cast<const uint8_t*>(image); ts.emb = emb;
-        ts.K = K; ts.k_offset = k_offset; ts.tiles_per_split = per; ts.l2norm = l2norm; ts.t_inv = t_inv;
-        ts.seed = seed; ts.offset = offset; ts.row_offset = row_offset;
-        ts.keys = reinterpret_cast<unsigned long long*>(keys); ts.n_events = n_resolved; ts.debug = prm.debug;
-        // warm start: scan the first eighth of the CTA's tiles for the row's best group before testing
-        ts.scout_tiles = std::min(per, std::max(0, env_int("B200VQ_TS_SCOUT", per >= 16 ? per / 8 : (per >= 8 ? 1 : 0))));
-        ts.flush_early = std::max(1, env_int("B200VQ_TS_FLUSH_EARLY", 8));
-        ts.flush_late = std::max(1, env_int("B200VQ_TS_FLUSH_LATE", 32));
-        ts.early_iters = env_int("B200VQ_TS_EARLY_ITERS", 2);
-        B200VQ_DISPATCH_DTYPE(z_dtype, T, {
-            switch (D) {
-                case 8: rc = launch_ts<8, T>(ts, grid, st); break;
-                case 16: rc = launch_ts<16, T>(ts, grid, st); break;
-                case 24: rc = launch_ts<24, T>(ts, grid, st); break;
-                default: rc = launch_ts<32, T>(ts, grid, st); break;
-            }
-        });
-        return rc;
-    }
+    if (mode == B200VQ_MODE_SAMPLE)
+        return launch_tc_sample(z, z_dtype, z_row_stride, N, D, image, emb, K, k_offset, l2norm, t_inv, seed, offset, nullptr,
+                                row_offset, keys, n_resolved, st);
+#define B200VQ_TC_DET(DD)                                                                         \
+    if (mode == B200VQ_MODE_ARGMIN_DIST) rc = launch_tc<DD, T, B200VQ_MODE_ARGMIN_DIST>(prm, grid, st); \
+    else rc = launch_tc<DD, T, B200VQ_MODE_ARGMAX_COS>(prm, grid, st)
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
         switch (D) {
-            case 8: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<8, T, MM>(prm, grid, st); }); break; }
-            case 16: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<16, T, MM>(prm, grid, st); }); break; }
-            case 24: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<24, T, MM>(prm, grid, st); }); break; }
-            default: { B200VQ_DISPATCH_MODE(mode, MM, { rc = launch_tc<32, T, MM>(prm, grid, st); }); break; }
+            case 8: B200VQ_TC_DET(8); break;
+            case 16: B200VQ_TC_DET(16); break;
+            case 24: B200VQ_TC_DET(24); break;
+            default: B200VQ_TC_DET(32); break;
         }
     });
-    if (rc || mode == B200VQ_MODE_SAMPLE || prm.debug) return rc;
+#undef B200VQ_TC_DET
+    if (rc || prm.debug) return rc;
     // exact re-scoring of undecided rows (deterministic modes)
     const unsigned int* flags = reinterpret_cast<const unsigned int*>(
         static_cast<const char*>(image) + static_cast<size_t>(total_tiles) * tc_tile_bytes(D));
@@ -171,7 +214,7 @@ int b200vq_scores_tc(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
 #undef B200VQ_GROUPS
     rc = launch_check();
     if (rc) return rc;
-    const unsigned rblocks = static_cast<unsigned>(kRescoreSegs * std::min<int64_t>(N, 2ll * sms));
+    const unsigned rblocks = static_cast<unsigned>(kRescoreSegs * std::min<int64_t>(N, 2ll * sm_count()));
 #define B200VQ_RESOLVE(DD, MM)                                                                                \
     rescore_kernel<DD, T, MM><<<rblocks, 256, 0, st>>>(static_cast<const T*>(z), z_row_stride, emb, e2, K,    \
                                                         k_offset, l2norm, k64, list, n_resolved)

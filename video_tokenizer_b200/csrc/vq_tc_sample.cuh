@@ -73,6 +73,9 @@ struct TsParams {
     unsigned int* n_events;   // nullable: += groups expanded (statistics)
     int debug;                // tuning aid: 1 = no MMA, 2 = no epilogue work, 64 = candidates dropped
     int flush_early, flush_late, early_iters;   // smallest batch drained at a tile end (first iterations / later)
+    // Philox (seed, offset) read on the DEVICE when non-null (CUDA-graph replays then draw fresh noise): [0] seed,
+    // [1] offset (the host code advances it with a one-thread kernel after this launch)
+    const unsigned long long* philox_dev;
 };
 
 // ---- expand up to 32 queued groups, one per lane.  Per code of the group the bound test is repeated against the
@@ -199,6 +202,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams
     const int scout = min(p.scout_tiles, ntiles);
     const int iters = ntiles + scout;           // iteration j: tile j (scan only while j < scout), then tiles 0..scout-1 again
     const uint32_t first_code = static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes;
+    const uint64_t seed = p.philox_dev ? p.philox_dev[0] : p.seed, offset = p.philox_dev ? p.philox_dev[1] : p.offset;
 
     const uint32_t bar_full = smem_u32(s_bar), bar_empty = bar_full + 8 * kTsStages;
     const uint32_t bar_tfull = bar_empty + 8 * kTsStages, bar_tempty = bar_tfull + 8 * kTsBufs;
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams
         auto read_nthr = [&]() { return fmaf(key_value(s_key[row_local]), kLog2e, -slack19); };
         auto flush = [&](uint32_t n) {
             ts_flush<D>(q_sc, q_meta, qhead, n, lane, row_base, s_z, s_key, p.emb, k_off32, k_end_global, grow0, p.t_inv, tl2e,
-                        slack19, p.seed, p.offset);
+                        slack19, seed, offset);
             qhead += n;
         };
         float nthr = -INFINITY;      // "everything can matter" until the row has a key
@@ -334,7 +338,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams
             Philox4 r0{};
             if (!scan_only) {
                 // before the accumulator is needed: 16 random bits for each of the 8 groups (one Philox call)
-                r0 = group_head_words(group0 >> 3, grow, p.seed, p.offset);
+                r0 = group_head_words(group0 >> 3, grow, seed, offset);
                 nthr = read_nthr();
             }
             mbar_wait_hint(bar_tfull + 8 * buf, (j >> 1) & 1);
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams
                     // last scan: expand the row's best approximate code of this group's columns -> a
                     // near-final threshold for the row
                     const uint32_t code = scode + (__float_as_uint(sbest) & 31u), g = code >> 3, pos = code & 7u;
-                    const Philox4 hw = group_head_words(g >> 3, grow, p.seed, p.offset);
+                    const Philox4 hw = group_head_words(g >> 3, grow, seed, offset);
                     const uint32_t slot = atomicAdd(s_qtail + warp, 1u) & (kTsQueueSlots - 1);
                     // scores: +inf for the chosen code (passes every test of the expansion), -inf for the other seven
                     uint32_t hw4[4] = {0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u};

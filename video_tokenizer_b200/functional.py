@@ -517,7 +517,7 @@ class _BottleneckFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w_in, b_in, weight, w_out, b_out, cfg):
-        mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset = cfg
+        mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset, philox_dev = cfg
         ctx.set_materialize_grads(False)   # unused outputs arrive as None, not as zero tensors
         lib = _lib.load()
         dev = x.device
@@ -544,7 +544,7 @@ class _BottleneckFunction(torch.autograd.Function):
                 mode, int(l2norm), t_inv, seed, offset, n_first, beta, w_cb, use_tc, z.data_ptr(), emb.data_ptr(),
                 wnorm.data_ptr(), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(), hists[0].data_ptr(),
                 hists[1].data_ptr(), losses.data_ptr(), usage.data_ptr(), norms.data_ptr(), out.data_ptr(), C, ws.data_ptr(), ws.numel(),
-                _stream())
+                _ptr(philox_dev), _stream())
             _lib.check(rc, "b200vq_bottleneck_forward")
         ctx.save_for_backward(x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste)
         ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
@@ -629,8 +629,10 @@ def bottleneck_supported(x, w_in, weight, w_out) -> bool:
             and bool(_lib.load().b200vq_linear_supported(w_out.shape[0], D)) and w_out.shape[0] == C)
 
 
-def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset):
+def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset,
+                    philox_dev=None):
     """-> (output, projected_z, znorm, emb, ste, idx(N,), loss_q, loss_commit, loss_codebook (0-dim each),
-    hists(2,K) [batch, first], usage(4), input norms(2))"""
-    cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset))
+    hists(2,K) [batch, first], usage(4), input norms(2)).  philox_dev: optional int64[2] DEVICE tensor {seed, offset}
+    read (and advanced) on the GPU instead of `seed` / `offset` -- what makes a captured CUDA graph replayable."""
+    cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset), philox_dev)
     return _BottleneckFunction.apply(x, w_in, b_in, weight, w_out, b_out, cfg)
