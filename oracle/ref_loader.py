@@ -1,9 +1,10 @@
 """Import the UNMODIFIED reference ``models/bottleneck.py`` (build container only).
 
-TEST INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box, so nothing
-that runs there (gpu tests, smoke, bench) may call this; it is used by
-``oracle/make_golden.py`` to produce ``tests/golden/*.npz`` and by the optional
-container-only cross-check in ``tests/test_oracle_golden.py``.
+TEST INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box; there the two files
+come from ``baseline/_ref`` (staged by ``oracle/stage_ref.py``, git-ignored, shipped with the
+snapshot).  Used by ``oracle/make_golden.py`` to produce ``tests/golden/*.npz``, by the
+cross-check in ``tests/test_oracle_golden.py`` and by the CPU legs of ``bench.py`` (the
+reference arm times this module itself: ``cpu_baseline.kind = "reference"``).
 
 ``import models`` on the reference fails (timm/easydict/vjepa2 absent),
 so the two files the path needs are executed under a stub ``models`` package that
@@ -19,7 +20,8 @@ import types
 
 
 def reference_root() -> str | None:
-    for cand in (os.environ.get("VT_REFERENCE_ROOT"), "/root/reference"):
+    staged = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
+    for cand in (os.environ.get("VT_REFERENCE_ROOT"), "/root/reference", staged):
         if cand and os.path.isfile(os.path.join(cand, "models", "bottleneck.py")):
             return cand
     return None
