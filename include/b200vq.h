@@ -299,6 +299,14 @@ int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t 
  *   backward outputs (each nullable = not needed): grad_x (N,C; ldgx), grad_w_in (D,C), grad_b_in (D),
  *            grad_weight (K,D), grad_w_out (C,D), grad_b_out (C)
  *   workspace >= b200vq_bottleneck_workspace_bytes(N,C,D,K), 16-byte aligned, same buffer both ways
+ *   act_dtype (B200VQ_DT_*): element type of z ('projected_z'), out ('output') and g_out -- fp32, or the caller's
+ *            autocast dtype (bf16 / fp16): under torch.autocast the reference's nn.Linears hand back that dtype while
+ *            x, the quantizer's tensors and every gradient this call returns stay fp32 (SURVEY.md 8b "dtype flow under
+ *            AMP"; trainers/larp_tokenizer_trainer.py:218-227, 244).  The contractions keep fp32 accumulation; the 2-byte
+ *            outputs are rounded once, from the fp32 result.
+ *   add (forward, nullable; add_rows rows of C fp32): a table added to 'output' in the out_linear store, row
+ *            (token index % add_rows) -- the tokenizer's `z + decoder_latent_pe` (models/larp_tokenizer.py:463-464) for
+ *            callers that want it folded into this pass.
  *   philox_dev (forward, nullable): DEVICE {seed, offset} (2 x uint64).  When given (stochastic mode on the
  *            tensor-core path only) it overrides seed / offset and the library adds 4 to the offset on the device
  *            after the draw (a one-thread kernel) -- the host-side generator advance of functional.philox_state, moved to the GPU so that a
@@ -308,11 +316,12 @@ size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K);
 int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
                               const float* weight, int64_t K, int D, const float* w_out, const float* b_out, int mode,
                               int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
-                              float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
+                              float w_cb, int use_tc, void* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
-                              float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
-                              uint64_t* philox_dev, b200vq_stream_t stream);
-int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
+                              float* norms2, void* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                              uint64_t* philox_dev, int act_dtype, const float* add, int64_t add_rows,
+                              b200vq_stream_t stream);
+int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, const float* g_losses, const float* g_ste,
                                const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
                                int64_t N, int C, const float* w_in, const float* w_out, const float* emb,
                                const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,

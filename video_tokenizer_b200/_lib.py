@@ -65,8 +65,8 @@ SIGNATURES = {
     "b200vq_gather_owned": (_i32, [_vp, _i64, _vp, _i64, _i64, _i32, _vp, _vp]),
     "b200vq_bottleneck_workspace_bytes": (_sz, [_i64, _i32, _i32, _i64]),
     "b200vq_bottleneck_forward": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _f32,
-                                         _u64, _u64, _i64, _f32, _f32, _i32] + [_vp] * 13 + [_i64, _vp, _sz, _vp, _vp]),
-    "b200vq_bottleneck_backward": (_i32, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32] + [_vp] * 8
+                                         _u64, _u64, _i64, _f32, _f32, _i32] + [_vp] * 13 + [_i64, _vp, _sz, _vp, _i32, _vp, _i64, _vp]),
+    "b200vq_bottleneck_backward": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32] + [_vp] * 8
                                    + [_i64, _i32, _i32, _f32, _f32, _vp, _i64] + [_vp] * 6 + [_sz, _vp]),
 }
 

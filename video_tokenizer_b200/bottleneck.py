@@ -344,7 +344,10 @@ class Bottleneck(nn.Module):
             last = torch.linalg.vector_norm(x[:, -1, :].float(), dim=-1).mean()
         return (first.item(), last.item()) if self.sync_diagnostics else (first, last)
 
-    def forward(self, x):
+    def forward(self, x, add=None):
+        """Reference Bottleneck.forward (bottleneck.py:170-188).  `add` (optional, B200 extra): an (n, C) table added to
+        'output' inside the out_linear store -- the tokenizer's `z + decoder_latent_pe` (models/larp_tokenizer.py:463-464)
+        for callers that want that pass folded in; treated as a constant (it is a buffer in every shipped config)."""
         reg = self.regularizer
         if (self.norm is None and type(reg) is SimpleVectorQuantizer and reg.entropy_loss_weight == 0
                 and self.project_dim == self.bottleneck_dim and len(x.shape) == 3 and self.in_linear.bias is not None
@@ -355,7 +358,7 @@ class Bottleneck(nn.Module):
                 x, self.in_linear.weight, self.in_linear.bias, reg.embedding.weight, self.out_linear.weight,
                 self.out_linear.bias, mode=mode, l2norm=reg.l2_normalized, t_inv=t_inv, beta=reg.beta,
                 w_cb=reg.codebook_loss_weight, n_first=x.shape[1], seed=seed, offset=offset,
-                philox_dev=reg.philox_dev if mode == _lib.MODE_SAMPLE else None)
+                philox_dev=reg.philox_dev if mode == _lib.MODE_SAMPLE else None, add=add)
             regularized_output = reg._assemble(projected_z.shape, znorm, emb, ste, idx, (lq, lc, lcb), hists[0], hists[1], usage)
             bottleneck_rep = regularized_output.pop("bottleneck_rep")
             input_norm_first, input_norm_last = norms[0], norms[1]
@@ -377,6 +380,8 @@ class Bottleneck(nn.Module):
         else:
             regularized_output = {"regularized_z": z}
         x_hat = self.project_out(regularized_output["regularized_z"])
+        if add is not None:
+            x_hat = x_hat + add.detach()
         bottleneck_rep = regularized_output.pop("bottleneck_rep")  # KeyError without a regularizer, as in the reference
         return {
             "output": x_hat,

@@ -377,11 +377,12 @@ size_t b200vq_bottleneck_workspace_bytes(int64_t N, int C, int D, int64_t K) {
 int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, const float* w_in, const float* b_in,
                               const float* weight, int64_t K, int D, const float* w_out, const float* b_out, int mode,
                               int l2norm, float t_inv, uint64_t seed, uint64_t offset, int64_t n_first, float beta,
-                              float w_cb, int use_tc, float* z, float* emb, float* wnorm, float* znorm, float* ste,
+                              float w_cb, int use_tc, void* z, float* emb, float* wnorm, float* znorm, float* ste,
                               int64_t* idx, float* zlen, int32_t* hist, int32_t* hist_first, float* losses, float* usage4,
-                              float* norms2, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
-                              uint64_t* philox_dev, b200vq_stream_t stream) {
-    if (N <= 0 || K <= 0 || !valid_mode(mode)) return B200VQ_EINVAL;
+                              float* norms2, void* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                              uint64_t* philox_dev, int act_dtype, const float* add, int64_t add_rows,
+                              b200vq_stream_t stream) {
+    if (N <= 0 || K <= 0 || !valid_mode(mode) || !valid_dtype(act_dtype)) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !weight || !w_out || !z || !emb || !wnorm || !znorm || !ste || !idx || !zlen || !hist || !hist_first ||
         !losses || !out)
@@ -392,7 +393,7 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
     char* ws = static_cast<char*>(workspace);
     float* e2 = reinterpret_cast<float*>(ws + l.e2);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, true, st);
+    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, act_dtype, true, st);
     if (rc) return rc;
     if (norms2) {
         if (n_first <= 0 || N % n_first) return B200VQ_EINVAL;
@@ -406,22 +407,22 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
         image = ws + l.image;
         if ((rc = b200vq_prepare_codebook_tc(emb, K, D, image, stream))) return rc;
     }
-    rc = forward_impl(z, B200VQ_DT_F32, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset,
+    rc = forward_impl(z, act_dtype, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset,
                       reinterpret_cast<unsigned long long*>(philox_dev), n_first, beta, w_cb, znorm, ste, idx, zlen, hist,
                       hist_first, losses, ws + l.vq, b200vq_workspace_bytes(N, D, K), st);
     if (rc) return rc;
     if (usage4 && (rc = b200vq_usage_stats(hist_first, hist, K, usage4, stream))) return rc;
-    return b200vq_linear_out(ste, N, D, w_out, 0, b_out, C, out, ldo, stream);
+    return launch_linear_out(ste, N, D, w_out, 0, b_out, C, out, act_dtype, ldo, nullptr, 0, 0, add, add_rows, nullptr, st);
 }
 
-int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_losses, const float* g_ste,
+int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, const float* g_losses, const float* g_ste,
                                const float* g_znorm, const float* g_emb, const float* g_z, const float* x, int64_t ldx,
                                int64_t N, int C, const float* w_in, const float* w_out, const float* emb,
                                const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,
                                const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
                                int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
                                float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
-    if (N <= 0 || K <= 0) return B200VQ_EINVAL;
+    if (N <= 0 || K <= 0 || !valid_dtype(act_dtype)) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !w_out || !emb || !wnorm || !znorm || !zlen || !idx || !ste) return B200VQ_EINVAL;
     const BnLayout l = bn_layout(N, C, D, K);
@@ -439,13 +440,15 @@ int b200vq_bottleneck_backward(const float* g_out, int64_t ldg, const float* g_l
         static const bool split_env = std::getenv("B200VQ_GRAD_OUT_SPLIT") != nullptr;   // tuning aid: the two-kernel path
         if (grad_w_out && !split_env && b200vq_grad_out_supported(C, D)) {
             // one pass over g_out: grad_a (+ g_ste), grad_W_out and grad_b_out together
-            if ((rc = b200vq_grad_out(g_out, ldg, ste, w_out, N, C, D, g_ste, ga, grad_w_out, grad_b_out, wgp,
-                                      b200vq_weight_grad_workspace_bytes(C, D), stream)))
+            if ((rc = launch_grad_out(g_out, act_dtype, ldg, ste, w_out, N, C, D, g_ste, ga, grad_w_out, grad_b_out, wgp,
+                                      b200vq_weight_grad_workspace_bytes(C, D), st)))
                 return rc;
         } else {
-            if ((rc = launch_linear_in(g_out, ldg, N, C, w_out, 1, nullptr, D, ga, false, st))) return rc;
+            if (act_dtype != B200VQ_DT_F32) return B200VQ_EDIM;   // the two-kernel path reads fp32 gradients only
+            const float* g32 = static_cast<const float*>(g_out);
+            if ((rc = launch_linear_in(g32, ldg, N, C, w_out, 1, nullptr, D, ga, B200VQ_DT_F32, false, st))) return rc;
             if (g_ste && (rc = add_inplace(ga, g_ste, N * D, st))) return rc;
-            if (grad_w_out && (rc = launch_weight_grad(g_out, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, wgp, st))) return rc;
+            if (grad_w_out && (rc = launch_weight_grad(g32, ldg, ste, N, C, D, grad_w_out, 0, grad_b_out, wgp, st))) return rc;
         }
         ga_in = ga;
     } else {

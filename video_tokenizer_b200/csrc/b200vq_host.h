@@ -59,8 +59,15 @@ inline int set_smem(K kernel, size_t bytes) {
 }
 
 // ---- entry points of one translation unit used by another (b200vq_linear.cu -> b200vq.cu) ----------
+// y_dtype / g_dtype: B200VQ_DT_* of the activation the caller's autocast region uses (fp32 outside autocast)
 int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, int w_is_cd, const float* bias, int D,
-                     float* y, bool precise, cudaStream_t st);
+                     void* y, int y_dtype, bool precise, cudaStream_t st);
+int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, void* y,
+                      int y_dtype, int64_t ldy, const int64_t* gidx, int64_t gK, int gl2, const float* add, int64_t add_rows,
+                      int* bad_flag, cudaStream_t st);
+int launch_grad_out(const void* g, int g_dtype, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D,
+                    const float* ga_add, float* ga, float* dw, float* colsum, void* workspace, size_t workspace_bytes,
+                    cudaStream_t st);
 int launch_weight_grad(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw, int dw_is_dc,
                        float* colsum, float* partial, cudaStream_t st);
 

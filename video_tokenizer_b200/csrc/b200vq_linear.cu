@@ -19,8 +19,9 @@ int b200vq_linear_supported(int C, int D) {
 namespace b200vq {
 namespace host {
 int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, int w_is_cd, const float* bias, int D,
-                     float* y, bool precise, cudaStream_t st) {
-    if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
+                     void* y, int y_dtype, bool precise, cudaStream_t st) {
+    if (N < 0 || !valid_dtype(y_dtype)) return B200VQ_EINVAL;
+    if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!x || !w || !y || ldx < C) return B200VQ_EINVAL;
     if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w) & 15) ||
@@ -29,20 +30,25 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
     const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinInRows - 1) / kLinInRows, static_cast<int64_t>(sm_count())));
     int rc = B200VQ_OK;
-#define B200VQ_LIN_IN(DD)                                                                        \
-    if (precise) {                                                                               \
-        if ((rc = set_smem(linear_in_kernel<DD, true>, smem))) return rc;                        \
-        linear_in_kernel<DD, true><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y);  \
-    } else {                                                                                     \
-        if ((rc = set_smem(linear_in_kernel<DD, false>, smem))) return rc;                       \
-        linear_in_kernel<DD, false><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, y); \
+#define B200VQ_LIN_IN_T(DD, PP, OT)                                                              \
+    {                                                                                            \
+        if ((rc = set_smem(linear_in_kernel<DD, PP, OT>, smem))) return rc;                      \
+        linear_in_kernel<DD, PP, OT><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, static_cast<OT*>(y)); \
     }
+    // fp32 output: 3xTF32 when `precise` (the latents decide the code indices); the 2-byte outputs of an autocast
+    // region carry 8 / 11 significant bits, so one TF32 pass (11 bits in, fp32 accumulate) is already finer than them
+#define B200VQ_LIN_IN(DD)                                                                        \
+    if (y_dtype == B200VQ_DT_F32) {                                                              \
+        if (precise) B200VQ_LIN_IN_T(DD, true, float) else B200VQ_LIN_IN_T(DD, false, float)     \
+    } else if (y_dtype == B200VQ_DT_BF16) B200VQ_LIN_IN_T(DD, false, __nv_bfloat16)              \
+    else B200VQ_LIN_IN_T(DD, false, __half)
     switch (D) {
         case 8: B200VQ_LIN_IN(8); break;
         case 16: B200VQ_LIN_IN(16); break;
         case 24: B200VQ_LIN_IN(24); break;
         default: B200VQ_LIN_IN(32); break;
     }
+#undef B200VQ_LIN_IN_T
 #undef B200VQ_LIN_IN
     return launch_check();
 }
@@ -52,17 +58,22 @@ extern "C" {
 
 int b200vq_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float* w, const float* bias, int D, float* y,
                      b200vq_stream_t stream) {
-    return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, true, static_cast<cudaStream_t>(stream));
+    return launch_linear_in(x, ldx, N, C, w, 0, bias, D, y, B200VQ_DT_F32, true, static_cast<cudaStream_t>(stream));
 }
 
-namespace {
-int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
-                      int64_t ldy, const int64_t* gidx, int64_t gK, int gl2, const float* add, int64_t add_rows, int* bad_flag,
-                      cudaStream_t st) {
-    if (N < 0 || !b200vq_linear_supported(C, D)) return N < 0 ? B200VQ_EINVAL : B200VQ_EDIM;
+}  // extern "C"
+namespace b200vq {
+namespace host {
+int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, void* y,
+                      int y_dtype, int64_t ldy, const int64_t* gidx, int64_t gK, int gl2, const float* add, int64_t add_rows,
+                      int* bad_flag, cudaStream_t st) {
+    if (N < 0 || !valid_dtype(y_dtype)) return B200VQ_EINVAL;
+    if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (N == 0) return B200VQ_OK;
     if (!a || !w || !y || ldy < C) return B200VQ_EINVAL;
-    if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & 15) || (reinterpret_cast<uintptr_t>(w) & 15)) return B200VQ_EALIGN;
+    // rows are written 4 elements at a time: 16-byte (fp32) / 8-byte (bf16, fp16) aligned
+    if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & (y_dtype == B200VQ_DT_F32 ? 15 : 7)) || (reinterpret_cast<uintptr_t>(w) & 15))
+        return B200VQ_EALIGN;
     if (add && (add_rows <= 0 || (reinterpret_cast<uintptr_t>(add) & 15))) return add_rows <= 0 ? B200VQ_EINVAL : B200VQ_EALIGN;
     const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
     int lo_dbg = 0, lo_grid = 1;   // one 16-warp CTA per SM: the weight staging is paid once per SM
@@ -70,10 +81,16 @@ int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     if (const char* env = std::getenv("B200VQ_LO_GRID")) lo_grid = std::max(1, std::atoi(env));
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinRows - 1) / kLinRows, static_cast<int64_t>(lo_grid) * sm_count()));
     int rc = B200VQ_OK;
+#define B200VQ_LIN_OUT_T(DD, OT)                                                                  \
+    {                                                                                             \
+        if ((rc = set_smem(linear_out_kernel<DD, OT>, smem))) return rc;                          \
+        linear_out_kernel<DD, OT><<<blocks, kLinOutThreads, smem, st>>>(a, N, w, w_is_dc, bias, C, static_cast<OT*>(y), ldy, lo_dbg, \
+                                                                        gidx, gK, gl2, add, add_rows, bad_flag);                  \
+    }
 #define B200VQ_LIN_OUT(DD)                                                           \
-    if ((rc = set_smem(linear_out_kernel<DD>, smem))) return rc;                     \
-    linear_out_kernel<DD><<<blocks, kLinOutThreads, smem, st>>>(a, N, w, w_is_dc, bias, C, y, ldy, lo_dbg, gidx, gK, gl2, add, \
-                                                                add_rows, bad_flag)
+    if (y_dtype == B200VQ_DT_F32) B200VQ_LIN_OUT_T(DD, float)                        \
+    else if (y_dtype == B200VQ_DT_BF16) B200VQ_LIN_OUT_T(DD, __nv_bfloat16)          \
+    else B200VQ_LIN_OUT_T(DD, __half)
     switch (D) {
         case 8: B200VQ_LIN_OUT(8); break;
         case 16: B200VQ_LIN_OUT(16); break;
@@ -81,13 +98,16 @@ int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
         default: B200VQ_LIN_OUT(32); break;
     }
 #undef B200VQ_LIN_OUT
+#undef B200VQ_LIN_OUT_T
     return launch_check();
 }
-}  // namespace
+}  // namespace host
+}  // namespace b200vq
+extern "C" {
 
 int b200vq_linear_out(const float* a, int64_t N, int D, const float* w, int w_is_dc, const float* bias, int C, float* y,
                       int64_t ldy, b200vq_stream_t stream) {
-    return launch_linear_out(a, N, D, w, w_is_dc, bias, C, y, ldy, nullptr, 0, 0, nullptr, 0, nullptr,
+    return launch_linear_out(a, N, D, w, w_is_dc, bias, C, y, B200VQ_DT_F32, ldy, nullptr, 0, 0, nullptr, 0, nullptr,
                              static_cast<cudaStream_t>(stream));
 }
 
@@ -96,20 +116,20 @@ int b200vq_decode_project(const int64_t* idx, int64_t n, const float* weight, in
                           b200vq_stream_t stream) {
     if (n < 0 || K <= 0) return B200VQ_EINVAL;
     if (n > 0 && !idx) return B200VQ_EINVAL;
-    return launch_linear_out(weight, n, D, w_out, 0, b_out, C, out, ldo, idx, K, l2norm, add, add_rows, bad_flag,
+    return launch_linear_out(weight, n, D, w_out, 0, b_out, C, out, B200VQ_DT_F32, ldo, idx, K, l2norm, add, add_rows, bad_flag,
                              static_cast<cudaStream_t>(stream));
 }
 
 extern "C++" {
 namespace {
-template <int D, bool WITH_GA>
-int launch_grad_out_d(const float* g, int64_t ldg, const float* a, const float* w, int64_t N, int C, const float* ga_add, float* ga,
+template <int D, bool WITH_GA, typename GT = float>
+int launch_grad_out_d(const GT* g, int64_t ldg, const float* a, const float* w, int64_t N, int C, const float* ga_add, float* ga,
                       float* partial, unsigned blocks, cudaStream_t st) {
     const size_t smem = WITH_GA ? go_smem_bytes<D>(C) : go_smem_bytes_wgrad<D>();
     int rc = B200VQ_OK;
 #define B200VQ_GO(NS)                                                                       \
-    if ((rc = set_smem(grad_out_kernel<D, NS, WITH_GA>, smem))) return rc;                  \
-    grad_out_kernel<D, NS, WITH_GA><<<blocks, kGoThreads, smem, st>>>(g, ldg, a, w, N, ga_add, ga, partial)
+    if ((rc = set_smem(grad_out_kernel<D, NS, WITH_GA, GT>, smem))) return rc;              \
+    grad_out_kernel<D, NS, WITH_GA, GT><<<blocks, kGoThreads, smem, st>>>(g, ldg, a, w, N, ga_add, ga, partial)
     switch (C / kGoCols) {
         case 1: B200VQ_GO(1); break;
         case 2: B200VQ_GO(2); break;
@@ -200,13 +220,16 @@ int b200vq_grad_out_supported(int C, int D) {
     return grad_out_smem(C, D) <= 227 * 1024 ? 1 : 0;
 }
 
-int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D, const float* ga_add,
-                    float* ga, float* dw, float* colsum, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
-    if (N < 0) return B200VQ_EINVAL;
+}  // extern "C"
+namespace b200vq {
+namespace host {
+int launch_grad_out(const void* g, int g_dtype, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D,
+                    const float* ga_add, float* ga, float* dw, float* colsum, void* workspace, size_t workspace_bytes,
+                    cudaStream_t st) {
+    if (N < 0 || !valid_dtype(g_dtype)) return B200VQ_EINVAL;
     if (!b200vq_grad_out_supported(C, D)) return B200VQ_EDIM;
     if (!dw || !ga) return B200VQ_EINVAL;
     if (!workspace || workspace_bytes < b200vq_weight_grad_workspace_bytes(C, D)) return B200VQ_EINVAL;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = B200VQ_OK;
     if (N == 0) {
         if ((rc = cuda_check(cudaMemsetAsync(dw, 0, static_cast<size_t>(C) * D * sizeof(float), st)))) return rc;
@@ -214,21 +237,36 @@ int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_
         return B200VQ_OK;
     }
     if (!g || !a || !w_out || ldg < C) return B200VQ_EINVAL;
-    if ((ldg & 3) || (reinterpret_cast<uintptr_t>(g) & 15) || (reinterpret_cast<uintptr_t>(a) & 15) ||
+    // rows of g are fetched 16 bytes at a time
+    if ((ldg & (g_dtype == B200VQ_DT_F32 ? 3 : 7)) || (reinterpret_cast<uintptr_t>(g) & 15) || (reinterpret_cast<uintptr_t>(a) & 15) ||
         (reinterpret_cast<uintptr_t>(workspace) & 15))
         return B200VQ_EALIGN;
     const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kGoTok - 1) / kGoTok, static_cast<int64_t>(sm_count())));
     float* partial = static_cast<float*>(workspace);
-    switch (D) {
-        case 8: rc = launch_grad_out_d<8, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        case 16: rc = launch_grad_out_d<16, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        case 24: rc = launch_grad_out_d<24, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
-        default: rc = launch_grad_out_d<32, true>(g, ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;
+#define B200VQ_GO_T(GT)                                                                                                       \
+    switch (D) {                                                                                                              \
+        case 8: rc = launch_grad_out_d<8, true, GT>(static_cast<const GT*>(g), ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break;   \
+        case 16: rc = launch_grad_out_d<16, true, GT>(static_cast<const GT*>(g), ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break; \
+        case 24: rc = launch_grad_out_d<24, true, GT>(static_cast<const GT*>(g), ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break; \
+        default: rc = launch_grad_out_d<32, true, GT>(static_cast<const GT*>(g), ldg, a, w_out, N, C, ga_add, ga, partial, blocks, st); break; \
     }
+    if (g_dtype == B200VQ_DT_F32) { B200VQ_GO_T(float) }
+    else if (g_dtype == B200VQ_DT_BF16) { B200VQ_GO_T(__nv_bfloat16) }
+    else { B200VQ_GO_T(__half) }
+#undef B200VQ_GO_T
     if (rc) return rc;
     const int total = C * D + C;
     weight_grad_reduce_kernel<<<(total + 63) / 64, dim3(64, kWgRedY), 0, st>>>(partial, static_cast<int>(blocks), C, D, dw, 0, colsum);
     return launch_check();
+}
+}  // namespace host
+}  // namespace b200vq
+extern "C" {
+
+int b200vq_grad_out(const float* g, int64_t ldg, const float* a, const float* w_out, int64_t N, int C, int D, const float* ga_add,
+                    float* ga, float* dw, float* colsum, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+    return launch_grad_out(g, B200VQ_DT_F32, ldg, a, w_out, N, C, D, ga_add, ga, dw, colsum, workspace, workspace_bytes,
+                           static_cast<cudaStream_t>(stream));
 }
 
 namespace {

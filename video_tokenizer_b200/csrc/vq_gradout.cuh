@@ -31,10 +31,14 @@ __host__ __device__ constexpr size_t go_smem_bytes_wgrad() {   // WITH_GA = fals
 }
 template <int D>
 __host__ __device__ constexpr size_t go_smem_bytes(int C) {
-    // w [C][YS] | ring [3][32][256] | a tiles [3][32][YS] | grad_a partials [8 column groups][32][D]
+    // w [C][YS] | ring [3][32][256] (sized for fp32 g) | a tiles [3][32][YS] | grad_a partials [8 column groups][32][D]
     return (static_cast<size_t>(C) * wg_ystride<D>() + kGoRing * kGoTok * kGoCols + kGoRing * kGoTok * wg_ystride<D>() +
             8 * kGoTok * D) * 4;
 }
+// element of the streamed operand as fp32 (bf16 and fp16 values are exact tf32 operands: no rounding step)
+__device__ __forceinline__ float go_f32(float v) { return v; }
+__device__ __forceinline__ float go_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float go_f32(__half v) { return __half2float(v); }
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gmem_src, bool valid) {
     const int bytes = valid ? 16 : 0;     // src-size 0: the 16 bytes are zero-filled, nothing is read
@@ -43,20 +47,25 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gme
                  : "memory");
 }
 
-// swizzle of a ring row: XOR applied to the column index (floats) of local token row r
-__device__ __forceinline__ int go_swz(int r) { return ((r & 3) << 3) | (r & 4); }
+// swizzle of a ring row: XOR applied to the column index (elements) of local token row r.  It permutes whole
+// 16-byte groups inside a 128-byte segment: 4-element groups for fp32, 8-element groups for the 2-byte types.
+template <typename GT>
+__device__ __forceinline__ int go_swz(int r) {
+    return sizeof(GT) == 4 ? (((r & 3) << 3) | (r & 4)) : (((r & 3) << 4) | ((r & 4) << 1));
+}
 
 // WITH_GA = false: weight / bias gradient only (in_linear.weight.grad = gz^T x with g = x, a = gz): no w, no ga.
-template <int D, int NS, bool WITH_GA>
-__global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __restrict__ g, int64_t ldg, const float* __restrict__ a,
+template <int D, int NS, bool WITH_GA, typename GT = float>
+__global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const GT* __restrict__ g, int64_t ldg, const float* __restrict__ a,
                                                                  const float* __restrict__ w, int64_t N,
                                                                  const float* __restrict__ ga_add, float* __restrict__ ga,
                                                                  float* __restrict__ partial) {
     constexpr int NT = D / 8, YS = wg_ystride<D>(), C = NS * kGoCols;
     extern __shared__ float s_go[];
     float* s_w = s_go;                                   // [C][YS] tf32 bits (WITH_GA only)
-    float* s_ring = s_w + (WITH_GA ? C * YS : 0);        // [3][32][256] swizzled
-    float* s_a = s_ring + kGoRing * kGoTok * kGoCols;    // [3][32][YS]
+    GT* s_ring = reinterpret_cast<GT*>(s_w + (WITH_GA ? C * YS : 0));        // [3][32][256] swizzled
+    float* s_a = s_w + (WITH_GA ? C * YS : 0) + kGoRing * kGoTok * kGoCols;  // [3][32][YS]
+    constexpr int EPC = 16 / sizeof(GT);                 // elements per 16-byte cp.async
     float* s_ga = s_a + kGoRing * kGoTok * YS;           // [8][32][D]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gq = lane >> 2, t = lane & 3;
 
@@ -68,13 +77,14 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
     auto issue = [&](int j, int s, int slot, int aslot) {
         const int64_t tok0 = (static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(j) * gridDim.x) * kGoTok;
         const int nrows = static_cast<int>(min(static_cast<int64_t>(kGoTok), N - tok0));   // >= 1
-        const float* src = g + tok0 * ldg + s * kGoCols;
-        float* dst = s_ring + slot * (kGoTok * kGoCols);
+        const GT* src = g + tok0 * ldg + s * kGoCols;
+        GT* dst = s_ring + slot * (kGoTok * kGoCols);
+        constexpr int CPR = kGoCols / EPC;               // 16-byte groups per row
 #pragma unroll
-        for (int q = 0; q < kGoTok * kGoCols / 4 / kGoThreads; ++q) {
-            const int i = threadIdx.x + q * kGoThreads, r = i >> 6, c4 = i & 63;
+        for (int q = 0; q < kGoTok * CPR / kGoThreads; ++q) {
+            const int i = threadIdx.x + q * kGoThreads, r = i / CPR, cg = i % CPR;
             const bool ok = r < nrows;
-            cp_async16_zfill(dst + r * kGoCols + ((4 * c4) ^ go_swz(r)), src + (ok ? r : 0) * ldg + 4 * c4, ok);
+            cp_async16_zfill(dst + r * kGoCols + ((EPC * cg) ^ go_swz<GT>(r)), src + (ok ? r : 0) * ldg + EPC * cg, ok);
         }
         if (s == 0 && threadIdx.x < kGoTok * (D / 4)) {
             const int r = threadIdx.x / (D / 4), d4 = threadIdx.x - r * (D / 4);
@@ -127,7 +137,8 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
     };
 
     const int mt = warp & 1, kq = warp >> 1;
-    const int swz_b = go_swz(gq);   // rows 16 mt + gq and + 8 share their low three bits
+    const int swz_b = go_swz<GT>(gq);   // rows 16 mt + gq and + 8 share their low three bits
+    const int sw0 = go_swz<GT>(t), sw1 = go_swz<GT>(t + 4);   // swizzles of token rows 8 ks + t and 8 ks + t + 4
     int slot = 0, aslot = 0;
     for (int j = 0; j < ntiles; ++j) {
         const float* ta = s_a + aslot * (kGoTok * YS);
@@ -147,16 +158,16 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
                 }
                 __syncthreads();
             }
-            const float* tile = s_ring + slot * (kGoTok * kGoCols);
+            const GT* tile = s_ring + slot * (kGoTok * kGoCols);
             slot = slot == kGoRing - 1 ? 0 : slot + 1;
             // ---- grad_w / grad_b: rows = columns 16 warp + gq (+8), k = tokens
             const int col = 16 * warp + gq;
 #pragma unroll
             for (int ks = 0; ks < kGoTok / 8; ++ks) {
-                const float* r0 = tile + (8 * ks + t) * kGoCols;          // token 8 ks + t     : swizzle t << 3
-                const float* r1 = r0 + 4 * kGoCols;                       // token 8 ks + t + 4 : swizzle (t << 3) | 4
-                const float x0 = r0[col ^ (t << 3)], x1 = r0[(col + 8) ^ (t << 3)];
-                const float x2 = r1[col ^ ((t << 3) | 4)], x3 = r1[(col + 8) ^ ((t << 3) | 4)];
+                const GT* r0 = tile + (8 * ks + t) * kGoCols;             // token 8 ks + t
+                const GT* r1 = r0 + 4 * kGoCols;                          // token 8 ks + t + 4
+                const float x0 = go_f32(r0[col ^ sw0]), x1 = go_f32(r0[(col + 8) ^ sw0]);
+                const float x2 = go_f32(r1[col ^ sw1]), x3 = go_f32(r1[(col + 8) ^ sw1]);
                 cs[s][0] += x0 + x2;
                 cs[s][1] += x1 + x3;
                 const uint32_t a0 = tf32_op(x0), a1 = tf32_op(x1), a2 = tf32_op(x2), a3 = tf32_op(x3);
@@ -169,14 +180,14 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const float* __
             }
             if constexpr (!WITH_GA) continue;
             // ---- grad_a: rows = tokens 16 mt + gq (+8), k = columns 32 kq + 8 ks + t (+4) of this stage
-            const float* ra = tile + (16 * mt + gq) * kGoCols;
-            const float* rb = ra + 8 * kGoCols;
+            const GT* ra = tile + (16 * mt + gq) * kGoCols;
+            const GT* rb = ra + 8 * kGoCols;
             const float* wb = s_w + (s * kGoCols + 32 * kq) * YS;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
                 const int kc = 32 * kq + 8 * ks + t;   // (kc ^ swz_b) == ((32 kq + t) ^ swz_b) ^ (8 ks): bits 3-4 of 32 kq + t are 0
-                const uint32_t a0 = tf32_op(ra[kc ^ swz_b]), a1 = tf32_op(rb[kc ^ swz_b]);
-                const uint32_t a2 = tf32_op(ra[(kc + 4) ^ swz_b]), a3 = tf32_op(rb[(kc + 4) ^ swz_b]);
+                const uint32_t a0 = tf32_op(go_f32(ra[kc ^ swz_b])), a1 = tf32_op(go_f32(rb[kc ^ swz_b]));
+                const uint32_t a2 = tf32_op(go_f32(ra[(kc + 4) ^ swz_b])), a3 = tf32_op(go_f32(rb[(kc + 4) ^ swz_b]));
 #pragma unroll
                 for (int n = 0; n < NT; ++n) {
                     const uint32_t b0 = __float_as_uint(wb[(8 * ks + t) * YS + 8 * n + gq]);

@@ -58,6 +58,22 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 
+// Output element types of the streaming linears: fp32, or the caller's autocast dtype (bf16 / fp16) when the module
+// runs under torch.autocast -- the reference's nn.Linear hands back that dtype there (SURVEY.md 8b "dtype flow under AMP")
+__device__ __forceinline__ void store2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+__device__ __forceinline__ void store2(__nv_bfloat16* p, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b); }
+__device__ __forceinline__ void store2(__half* p, float a, float b) { *reinterpret_cast<__half2*>(p) = __floats2half2_rn(a, b); }
+// four consecutive outputs, streaming (evict-first) store
+__device__ __forceinline__ void store4_cs(float* p, float a, float b, float c, float d) { __stcs(reinterpret_cast<float4*>(p), make_float4(a, b, c, d)); }
+__device__ __forceinline__ void store4_cs(__nv_bfloat16* p, float a, float b, float c, float d) {
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+    __stcs(reinterpret_cast<uint2*>(p), make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi)));
+}
+__device__ __forceinline__ void store4_cs(__half* p, float a, float b, float c, float d) {
+    const __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+    __stcs(reinterpret_cast<uint2*>(p), make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi)));
+}
+
 // =======================================================================================
 // linear_in:  y[n][d] = sum_c x[n][c] * w[d][c] + b[d]      (x: N x C, row stride ldx; w: D x C, or C x D when w_is_cd)
 // One warp = 16 rows.  x streams straight from global memory into A fragments (one float4
@@ -68,10 +84,10 @@ constexpr int kLinRows = 128;  // token rows per CTA (8 warps x 16)
 constexpr int kLinInThreads = 512;                      // 16 warps share one staged weight matrix (1 CTA / SM)
 constexpr int kLinInRows = kLinInThreads;               // linear_in: 32 rows per warp (two m16 tiles share every w fragment)
 
-template <int D, bool PRECISE>
+template <int D, bool PRECISE, typename OT = float>
 __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
                                                         const float* __restrict__ w, int w_is_cd,
-                                                        const float* __restrict__ bias, float* __restrict__ y) {
+                                                        const float* __restrict__ bias, OT* __restrict__ y) {
     constexpr int NT = D / 8;
     extern __shared__ float s_w[];  // [D][C + 16]
     const int cs = C + 16;
@@ -164,8 +180,8 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
             const int d = 8 * j + 2 * t;
             const float b0 = bias ? __ldg(bias + d) : 0.f, b1 = bias ? __ldg(bias + d + 1) : 0.f;
             const int64_t ra = r0 + 16 * m, rb = ra + 8;
-            if (ra < N) *reinterpret_cast<float2*>(y + ra * D + d) = make_float2(acc[m][j][0] + b0, acc[m][j][1] + b1);
-            if (rb < N) *reinterpret_cast<float2*>(y + rb * D + d) = make_float2(acc[m][j][2] + b0, acc[m][j][3] + b1);
+            if (ra < N) store2(y + ra * D + d, acc[m][j][0] + b0, acc[m][j][1] + b1);
+            if (rb < N) store2(y + rb * D + d, acc[m][j][2] + b0, acc[m][j][3] + b1);
         }
     }   // tile
 }
@@ -177,10 +193,10 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
 // [C][D + 4] (conflict-free B fragments).  One warp = 16 rows x all C columns.
 // =======================================================================================
 constexpr int kLinOutThreads = 512;   // 16 warps share one staged weight matrix
-template <int D>
+template <int D, typename OT = float>
 __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float* __restrict__ a, int64_t N, const float* __restrict__ w,
                                                          int w_is_dc, const float* __restrict__ bias, int C,
-                                                         float* __restrict__ y, int64_t ldy, int dbg,
+                                                         OT* __restrict__ y, int64_t ldy, int dbg,
                                                          const int64_t* __restrict__ gidx = nullptr, int64_t gK = 0, int gl2 = 0,
                                                          const float* __restrict__ add = nullptr, int64_t add_rows = 0,
                                                          int* __restrict__ bad_flag = nullptr) {
@@ -257,8 +273,8 @@ __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float*
             pa = add + (min(r0, N - 1) % add_rows) * C + 4 * t;
             pb = add + (min(r0 + 8, N - 1) % add_rows) * C + 4 * t;
         }
-        float* ya = y + r0 * ldy + 4 * t;
-        float* yb = y + (r0 + 8) * ldy + 4 * t;
+        OT* ya = y + r0 * ldy + 4 * t;
+        OT* yb = y + (r0 + 8) * ldy + 4 * t;
         const bool oka = r0 < N, okb = r0 + 8 < N;
 #pragma unroll 2
         for (int j = j0; j < j1; ++j) {
@@ -274,12 +290,12 @@ __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float*
             const float4 bb = *reinterpret_cast<const float4*>(&s_b[16 * j + 4 * t]);
             if (add) {
                 const float4 ea = __ldg(reinterpret_cast<const float4*>(pa + 16 * j)), eb = __ldg(reinterpret_cast<const float4*>(pb + 16 * j));
-                if (oka) __stcs(reinterpret_cast<float4*>(ya + 16 * j), make_float4(acc0[0] + bb.x + ea.x, acc0[1] + bb.y + ea.y, acc1[0] + bb.z + ea.z, acc1[1] + bb.w + ea.w));
-                if (okb) __stcs(reinterpret_cast<float4*>(yb + 16 * j), make_float4(acc0[2] + bb.x + eb.x, acc0[3] + bb.y + eb.y, acc1[2] + bb.z + eb.z, acc1[3] + bb.w + eb.w));
+                if (oka) store4_cs(ya + 16 * j, acc0[0] + bb.x + ea.x, acc0[1] + bb.y + ea.y, acc1[0] + bb.z + ea.z, acc1[1] + bb.w + ea.w);
+                if (okb) store4_cs(yb + 16 * j, acc0[2] + bb.x + eb.x, acc0[3] + bb.y + eb.y, acc1[2] + bb.z + eb.z, acc1[3] + bb.w + eb.w);
                 continue;
             }
-            if (oka) __stcs(reinterpret_cast<float4*>(ya + 16 * j), make_float4(acc0[0] + bb.x, acc0[1] + bb.y, acc1[0] + bb.z, acc1[1] + bb.w));
-            if (okb) __stcs(reinterpret_cast<float4*>(yb + 16 * j), make_float4(acc0[2] + bb.x, acc0[3] + bb.y, acc1[2] + bb.z, acc1[3] + bb.w));
+            if (oka) store4_cs(ya + 16 * j, acc0[0] + bb.x, acc0[1] + bb.y, acc1[0] + bb.z, acc1[1] + bb.w);
+            if (okb) store4_cs(yb + 16 * j, acc0[2] + bb.x, acc0[3] + bb.y, acc1[2] + bb.z, acc1[3] + bb.w);
         }
     }
 }

@@ -312,12 +312,13 @@ def linear_dims_supported(C: int, D: int) -> bool:
     return LINEARS == "fused" and not torch.is_autocast_enabled() and bool(_lib.load().b200vq_linear_supported(C, D))
 
 
-def _rows2d(x: torch.Tensor) -> Tuple[torch.Tensor, int, int]:
+def _rows2d(x: torch.Tensor, gran: Optional[int] = None) -> Tuple[torch.Tensor, int, int]:
     """(tensor, row stride, N) for a (..., C) tensor viewed as N rows; copies unless row-uniform
-    with a 16-byte aligned base and a stride that is a multiple of 4 elements."""
+    with a 16-byte aligned base and a stride that is a multiple of `gran` elements (16 bytes' worth)."""
     C = x.shape[-1]
+    gran = gran or max(1, 16 // x.element_size())
     t, stride = rows_view(x) if x.dim() in (2, 3) else (x.contiguous(), C)
-    if stride % 4 or t.data_ptr() % 16:
+    if stride % gran or t.data_ptr() % 16:
         t, stride = x.contiguous(), C
     return t, stride, t.shape[:-1].numel()
 
@@ -517,7 +518,7 @@ class _BottleneckFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w_in, b_in, weight, w_out, b_out, cfg):
-        mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset, philox_dev = cfg
+        mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset, philox_dev, act_dtype, add = cfg
         ctx.set_materialize_grads(False)   # unused outputs arrive as None, not as zero tensors
         lib = _lib.load()
         dev = x.device
@@ -527,10 +528,18 @@ class _BottleneckFunction(torch.autograd.Function):
         lead = x.shape[:-1]
         f32 = dict(dtype=torch.float32, device=dev)
         with _on_device(dev):
-            out = torch.empty(*lead, C, **f32)
-            # one allocation for the (N, D) tensors: projected_z | znorm | ste
-            nd = torch.empty(3, *lead, D, **f32)
-            z, znorm, ste = nd[0], nd[1], nd[2]
+            out = torch.empty(*lead, C, dtype=act_dtype, device=dev)
+            # one allocation for the fp32 (N, D) tensors: [projected_z |] znorm | ste
+            if act_dtype is torch.float32:
+                nd = torch.empty(3, *lead, D, **f32)
+                z, znorm, ste = nd[0], nd[1], nd[2]
+            else:   # projected_z in the autocast dtype (models/bottleneck.py:140-142 under AMP)
+                nd = torch.empty(2, *lead, D, **f32)
+                z, znorm, ste = torch.empty(*lead, D, dtype=act_dtype, device=dev), nd[0], nd[1]
+            add_rows = 0
+            if add is not None:
+                add = add.detach().to(torch.float32).reshape(-1, C).contiguous()
+                add_rows = add.shape[0]
             emb = torch.empty(K, D, **f32)
             small = torch.empty(K + N + 12, **f32)          # wnorm | zlen | losses(3) usage(4) input norms(2)
             wnorm, zlen, losses, usage = small[:K], small[K:K + N], small[K + N:K + N + 3], small[K + N + 3:K + N + 7]
@@ -544,10 +553,10 @@ class _BottleneckFunction(torch.autograd.Function):
                 mode, int(l2norm), t_inv, seed, offset, n_first, beta, w_cb, use_tc, z.data_ptr(), emb.data_ptr(),
                 wnorm.data_ptr(), znorm.data_ptr(), ste.data_ptr(), idx.data_ptr(), zlen.data_ptr(), hists[0].data_ptr(),
                 hists[1].data_ptr(), losses.data_ptr(), usage.data_ptr(), norms.data_ptr(), out.data_ptr(), C, ws.data_ptr(), ws.numel(),
-                _ptr(philox_dev), _stream())
+                _ptr(philox_dev), _DTYPES[act_dtype], _ptr(add), add_rows, _stream())
             _lib.check(rc, "b200vq_bottleneck_forward")
         ctx.save_for_backward(x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste)
-        ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None)
+        ctx.cfg = (bool(l2norm), beta, w_cb, N, C, D, K, b_in is not None, b_out is not None, act_dtype)
         ctx.hists = hists
         ctx.mark_non_differentiable(idx, hists, usage, norms)
         # the three losses leave as separate 0-dim outputs: indexing a (3,) output in the caller would put a
@@ -557,7 +566,7 @@ class _BottleneckFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_out, g_z, g_znorm, g_emb, g_ste, _gi, g_lq, g_lc, g_lcb, _gh, _gu, _gn):
         x, w_in, w_out, emb, wnorm, znorm, zlen, idx, ste = ctx.saved_tensors
-        l2norm, beta, w_cb, N, C, D, K, has_b_in, has_b_out = ctx.cfg
+        l2norm, beta, w_cb, N, C, D, K, has_b_in, has_b_out, act_dtype = ctx.cfg
         lib = _lib.load()
         dev = x.device
 
@@ -570,7 +579,8 @@ class _BottleneckFunction(torch.autograd.Function):
         g_lq, g_lc, g_lcb = _f32c(g_lq), _f32c(g_lc), _f32c(g_lcb)
         go, ldg = None, C
         if g_out is not None:
-            go, ldg, _ = _rows2d(g_out.to(torch.float32))
+            # grad of 'output' arrives in the output's dtype (bf16 / fp16 under autocast) and is read as such
+            go, ldg, _ = _rows2d(g_out if g_out.dtype is act_dtype else g_out.to(act_dtype))
         need = ctx.needs_input_grad
         f32 = dict(dtype=torch.float32, device=dev)
         with _on_device(dev):
@@ -609,7 +619,7 @@ class _BottleneckFunction(torch.autograd.Function):
                 _lib.check(lib.b200vq_pack3(_ptr(g_lq), _ptr(g_lc), _ptr(g_lcb), g_losses.data_ptr(), _stream()), "b200vq_pack3")
             ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
             rc = lib.b200vq_bottleneck_backward(
-                _ptr(go), ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,
+                _ptr(go), _DTYPES[act_dtype], ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,
                 w_in.data_ptr(), w_out.data_ptr(), emb.data_ptr(), wnorm.data_ptr(), znorm.data_ptr(), zlen.data_ptr(),
                 idx.data_ptr(), ste.data_ptr(), K, D, int(l2norm), beta, w_cb, _ptr(gx), C, _ptr(gw_in), _ptr(gb_in), _ptr(gw),
                 _ptr(gw_out), _ptr(gb_out), ws.data_ptr(), ws.numel(), _stream())
@@ -617,22 +627,36 @@ class _BottleneckFunction(torch.autograd.Function):
         return gx, gw_in, gb_in, gw, gw_out, gb_out, None
 
 
+def autocast_act_dtype() -> torch.dtype:
+    """dtype the Bottleneck's linears hand back: the CUDA autocast dtype inside an autocast region, else fp32"""
+    if torch.is_autocast_enabled():
+        return torch.get_autocast_dtype("cuda") if hasattr(torch, "get_autocast_dtype") else torch.get_autocast_gpu_dtype()
+    return torch.float32
+
+
 def bottleneck_supported(x, w_in, weight, w_out) -> bool:
-    """The one-call path needs fp32 everything, contiguous parameters, no autocast and shapes the
-    streaming linear kernels take."""
+    """The one-call path needs fp32 x and parameters (under autocast the activations it hands back are bf16 / fp16, like
+    the reference's nn.Linears), contiguous parameters and shapes the streaming linear kernels take."""
     D, C = w_in.shape
+    act = autocast_act_dtype()
+    lib = _lib.load()
     return (LINEARS == "fused" and x.is_cuda and x.dim() == 3 and x.dtype == torch.float32
             and w_in.dtype == weight.dtype == w_out.dtype == torch.float32
             and w_in.is_contiguous() and weight.is_contiguous() and w_out.is_contiguous()
             and tuple(w_out.shape) == (w_out.shape[0], D) and weight.shape[1] == D
-            and not torch.is_autocast_enabled() and bool(_lib.load().b200vq_linear_supported(C, D))
-            and bool(_lib.load().b200vq_linear_supported(w_out.shape[0], D)) and w_out.shape[0] == C)
+            and act in _DTYPES and bool(lib.b200vq_linear_supported(C, D))
+            and (act is torch.float32 or bool(lib.b200vq_grad_out_supported(C, D)))
+            and bool(lib.b200vq_linear_supported(w_out.shape[0], D)) and w_out.shape[0] == C)
 
 
 def bottleneck_step(x, w_in, b_in, weight, w_out, b_out, *, mode, l2norm, t_inv, beta, w_cb, n_first, seed, offset,
-                    philox_dev=None):
+                    philox_dev=None, add=None):
     """-> (output, projected_z, znorm, emb, ste, idx(N,), loss_q, loss_commit, loss_codebook (0-dim each),
     hists(2,K) [batch, first], usage(4), input norms(2)).  philox_dev: optional int64[2] DEVICE tensor {seed, offset}
-    read (and advanced) on the GPU instead of `seed` / `offset` -- what makes a captured CUDA graph replayable."""
-    cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset), philox_dev)
+    read (and advanced) on the GPU instead of `seed` / `offset` -- what makes a captured CUDA graph replayable.
+    Inside torch.autocast, output / projected_z come back in the autocast dtype.  add: optional (n, C) table added to
+    `output` in the out_linear store (the decoder's latent positional embedding, models/larp_tokenizer.py:463-464); it is
+    treated as a constant (a buffer in every shipped config: learned_decoder_latent_pe = False)."""
+    cfg = (int(mode), bool(l2norm), float(t_inv), float(beta), float(w_cb), int(n_first), int(seed), int(offset), philox_dev,
+           autocast_act_dtype(), add)
     return _BottleneckFunction.apply(x, w_in, b_in, weight, w_out, b_out, cfg)
