@@ -312,6 +312,26 @@ def small_batch_leg(V, args, dev, sampler):
     return out
 
 
+def amp_leg(V, args, dev, sampler, ms_fp32):
+    """BASELINE configs[3]: the same step under bf16 autocast (projected_z / output / grad_output bf16, everything else
+    fp32) on the library's own kernels, graph-replayed"""
+    B, n, C = args.batch, CFG["n"], CFG["C"]
+    m = make_module(V, args, dev)
+    x = torch.randn(B, n, C, device=dev)
+    G = torch.randn(B, n, C, device=dev).to(torch.bfloat16)
+    step = V.GraphedBottleneckStep(m, x, G, loss_q_grad=CFG["loss_q_weight"], autocast_dtype=torch.bfloat16)
+    for _ in range(5):
+        step.replay()
+    t = time_events(step.replay, 30, sampler)
+    ok = step.out["output"].dtype is torch.bfloat16 and step.out["projected_z"].dtype is torch.bfloat16
+    m.regularizer.disable_device_rng()
+    N = B * n
+    bpt = step_bytes_per_token() - 2 * 2 * C - 2 * CFG["D"] * 2     # output and grad_output halve, projected_z too
+    return {"dtype": "bf16 activations (autocast), fp32 accumulate / quantizer / gradients", "ms_per_step": t,
+            "tokens_per_s": N / (t * 1e-3), "vs_fp32": ms_fp32 / t, "activation_dtypes_ok": bool(ok),
+            "step_hbm": {"bytes_per_token": bpt, "achieved_gbs": bpt * N / (t * 1e-3) / 1e9}}
+
+
 def tokenizer_leg(V, dev):
     """BASELINE configs[1]: unmodified LARPTokenizer (cfgs/larp_tokenizer.yaml bottleneck block, 16 x 128 x 128 clips,
     B = 8) fwd+bwd on this GPU: drop-in installed vs the reference's own bottleneck (eager torch) in the same tokenizer"""
@@ -646,7 +666,12 @@ def run_b200(args):
                 "exact_fp32_kernel": {"kernel_ms": ex_ms, "achieved_tflops": flops / (ex_ms * 1e-3) / 1e12,
                                       "peak_tflops_measured": fma_peak, "frac": flops / (ex_ms * 1e-3) / 1e12 / fma_peak}}
 
-    small = tok = None
+    small = tok = amp = None
+    if not args.no_extras and world == 1 and args.mode == "stochastic":
+        try:
+            amp = amp_leg(V, args, dev, sampler, ms_step)
+        except Exception as e:   # pragma: no cover
+            amp = {"error": f"{type(e).__name__}: {e}"[:300]}
     if not args.no_extras and world == 1:
         try:
             small = small_batch_leg(V, args, dev, sampler)
@@ -681,6 +706,7 @@ def run_b200(args):
                 "steps": e2e_steps},
         "gpu_launches": launches,
         "roofline": roofline,
+        "amp_bf16": amp,
         "small_batch": small,
         "tokenizer": tok,
         "codebook_sharded": cb_sharded,

@@ -23,10 +23,12 @@ class GraphedBottleneckStep:
     static tensors `self.out` (the module's output dict), `self.stats` (code-usage statistics), `self.x.grad` and the
     parameters' `.grad` (overwritten, not accumulated, on every replay)."""
 
-    def __init__(self, module, x: torch.Tensor, grad_output: torch.Tensor, loss_q_grad: float = 0.1, warmup: int = 3):
+    def __init__(self, module, x: torch.Tensor, grad_output: torch.Tensor, loss_q_grad: float = 0.1, warmup: int = 3,
+                 autocast_dtype: Optional[torch.dtype] = None):
         if not x.is_cuda:
             raise RuntimeError("GraphedBottleneckStep needs CUDA tensors")
         self.module = module
+        self.autocast_dtype = autocast_dtype   # bf16 / fp16: the step runs inside torch.autocast (grad_output in that dtype)
         self.reg = module.regularizer
         self.x = x.detach().clone().requires_grad_(True)
         self.g = grad_output.detach().clone()
@@ -49,7 +51,11 @@ class GraphedBottleneckStep:
         self.reg.enable_device_rng(x.device)   # re-synchronise with the generator: the warm-up advanced the device state
 
     def _step(self):
-        out = self.module(self.x)
+        if self.autocast_dtype is not None:
+            with torch.autocast("cuda", dtype=self.autocast_dtype):
+                out = self.module(self.x)
+        else:
+            out = self.module(self.x)
         stats = self.reg.code_usage() if hasattr(self.reg, "code_usage") else None
         torch.autograd.backward([out["output"], out["loss_q"]], [self.g, self.gq])
         return out, stats
