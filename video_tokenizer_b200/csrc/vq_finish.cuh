@@ -122,14 +122,17 @@ __global__ void __launch_bounds__(128) backward_kernel(const float* __restrict__
         if (g_ste) gv = gs4[d / 4];
         if (g_zn) { const float4 t = gz4[d / 4]; gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w; }
         const float zz[4] = {zv.x, zv.y, zv.z, zv.w}, qq[4] = {qv.x, qv.y, qv.z, qv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+        float sc[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             zn[d + e] = zz[e];
             const float g = a * (zz[e] - qq[e]) + gg[e];
             dzh[d + e] = g;
             proj = fmaf(zz[e], g, proj);
-            if (b != 0.f && owned) atomicAdd(grad_emb + code * D + d + e, b * (qq[e] - zz[e]));
+            sc[e] = b * (qq[e] - zz[e]);
         }
+        // codebook-loss gradient scatter-add: one 16-byte vector reduction per four elements (red.global.add.v4.f32)
+        if (b != 0.f && owned) atomicAdd(reinterpret_cast<float4*>(grad_emb + code * D + d), make_float4(sc[0], sc[1], sc[2], sc[3]));
     }
     GT* out = grad_z + row * D;
     if (l2norm) {

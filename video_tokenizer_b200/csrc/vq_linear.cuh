@@ -47,6 +47,19 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// D (+)= A B with bf16 operands, k = 16.  Fragment layout (g = lane >> 2, t = lane & 3), two bf16 per register:
+//   A: a0 (row g, k 2t..2t+1)  a1 (row g+8, same k)  a2 (row g, k 2t+8..2t+9)  a3 (row g+8, same k)
+//   B: b0 (k 2t..2t+1, col g)  b1 (k 2t+8..2t+9, col g)          C: as m16n8k8
+__device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
                  "l"(gmem_src)
@@ -126,14 +139,26 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
         for (int u = 0; u < PF; ++u) {
             const int c = c0 + u;
             if (c >= chunks) break;
-            uint32_t xb[4][4], xs[4][4];   // [row q][column 4t + e]
+            // PRECISE: x.w ~ xb.wb (TF32 x TF32, exact products) + xs.wb + xb.ws with the two correction products on
+            // bf16 operands (k = 16 per MMA: 4 MMAs per 16 columns instead of 6).  xb is x as the tensor core sees it
+            // (low 13 mantissa bits ignored), xs = x - xb exactly; the corrections are 2^-10 of the result, so their
+            // bf16 operand rounding (2^-8) costs ~2^-19 of it: still fp32-class (referee tests: rel_err(z) < 2e-6).
+            uint32_t xb[4][4];             // [row q][column 4t + e]: main operand bits
+            uint32_t xsp[4][2], xbp[4][2]; // bf16 pairs (columns 4t, 4t+1 | 4t+2, 4t+3) of the small / big parts
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float4 a = v[u][q];
                 if (c + PF < chunks) v[u][q] = __ldg(xr[q] + 4 * (c + PF));
                 if constexpr (PRECISE) {
-                    tf32_split(a.x, xb[q][0], xs[q][0]); tf32_split(a.y, xb[q][1], xs[q][1]);
-                    tf32_split(a.z, xb[q][2], xs[q][2]); tf32_split(a.w, xb[q][3], xs[q][3]);
+                    const float e[4] = {a.x, a.y, a.z, a.w};
+                    float sm[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        xb[q][i] = __float_as_uint(e[i]);
+                        sm[i] = e[i] - __uint_as_float(xb[q][i] & 0xFFFFE000u);
+                    }
+                    xsp[q][0] = pack_bf16(sm[0], sm[1]); xsp[q][1] = pack_bf16(sm[2], sm[3]);
+                    xbp[q][0] = pack_bf16(e[0], e[1]); xbp[q][1] = pack_bf16(e[2], e[3]);
                 } else {
                     xb[q][0] = tf32_op(a.x); xb[q][1] = tf32_op(a.y); xb[q][2] = tf32_op(a.z); xb[q][3] = tf32_op(a.w);
                 }
@@ -144,18 +169,20 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
                 if constexpr (PRECISE) {
                 uint32_t wb[4], ws[4];
                 tf32_split(wv.x, wb[0], ws[0]); tf32_split(wv.y, wb[1], ws[1]); tf32_split(wv.z, wb[2], ws[2]); tf32_split(wv.w, wb[3], ws[3]);
-                // step 0: columns 4t, 4t+1 ; step 1: columns 4t+2, 4t+3.  The tensor core adds into
-                // its accumulator with truncation, so every chunk starts from zero accumulators
-                // (one for the big.big terms, one for the corrections) and the running sum is kept
-                // in fp32 round-to-nearest on the CUDA cores.
+                const uint32_t wbp0 = pack_bf16(wv.x, wv.y), wbp1 = pack_bf16(wv.z, wv.w);
+                const uint32_t wsp0 = pack_bf16(__uint_as_float(ws[0]), __uint_as_float(ws[1]));
+                const uint32_t wsp1 = pack_bf16(__uint_as_float(ws[2]), __uint_as_float(ws[3]));
+                // TF32 steps: step 0 = columns 4t, 4t+1 ; step 1 = columns 4t+2, 4t+3.  bf16 MMA: k 2t..2t+1 = columns
+                // 4t, 4t+1 and k 2t+8..2t+9 = columns 4t+2, 4t+3 (the same column permutation on both operands).  The
+                // tensor core adds into its accumulator with truncation, so every chunk starts from zero accumulators
+                // (one for the big.big terms, one for the corrections) and the running sum is kept in fp32
+                // round-to-nearest on the CUDA cores.
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {
                     const int qa = 2 * m, qb = 2 * m + 1;
                     float cm[4] = {0.f, 0.f, 0.f, 0.f}, cc[4] = {0.f, 0.f, 0.f, 0.f};
-                    mma_tf32(cc, xs[qa][0], xs[qb][0], xs[qa][1], xs[qb][1], wb[0], wb[1]);
-                    mma_tf32(cc, xb[qa][0], xb[qb][0], xb[qa][1], xb[qb][1], ws[0], ws[1]);
-                    mma_tf32(cc, xs[qa][2], xs[qb][2], xs[qa][3], xs[qb][3], wb[2], wb[3]);
-                    mma_tf32(cc, xb[qa][2], xb[qb][2], xb[qa][3], xb[qb][3], ws[2], ws[3]);
+                    mma_bf16(cc, xsp[qa][0], xsp[qb][0], xsp[qa][1], xsp[qb][1], wbp0, wbp1);
+                    mma_bf16(cc, xbp[qa][0], xbp[qb][0], xbp[qa][1], xbp[qb][1], wsp0, wsp1);
                     mma_tf32(cm, xb[qa][0], xb[qb][0], xb[qa][1], xb[qb][1], wb[0], wb[1]);
                     mma_tf32(cm, xb[qa][2], xb[qb][2], xb[qa][3], xb[qb][3], wb[2], wb[3]);
 #pragma unroll
