@@ -1,16 +1,9 @@
-// b200vq -- the tcgen05 scoring kernel (see vq_tc.cuh for the design).
+// b200vq -- the tcgen05 scoring kernel of the DETERMINISTIC modes (see vq_tc.cuh for the design; the stochastic
+// mode has its own kernel, vq_tc_sample.cuh).
 //
-// Epilogue structure (both modes).  A thread owns one token row and sees its scores 32
-// columns at a time (tcgen05.ld 32x32b.x32).  Per group of 8 codes it does a few branch-free
-// instructions (3-input max tree + one compare) that decide whether the group can matter:
-//   deterministic: group max within kTcMargin of the row's best so far;
-//   stochastic:    16 random bits of the group's largest Gumbel say its bound can beat the
-//                  row's best perturbed score so far.
-// Groups that can matter are rare after the first few tiles, and rows of one warp hit them
-// at different times, so they are not processed in place (that would idle 31 lanes): the
-// lane pushes (group id, 8 scores) into its warp's shared-memory queue, and whenever 32
-// entries are queued the warp processes them one per lane with all lanes busy, merging
-// results into per-row keys in shared memory with atomics.
+// Epilogue structure.  A thread owns one token row and sees its scores 32 columns at a time (tcgen05.ld 32x32b.x32).
+// Per group of 8 codes it does a few branch-free instructions (3-input max tree, position tags in the low mantissa
+// bits) that keep the row's best and second-best group maxima; the winning code is resolved afterwards in exact fp32.
 #pragma once
 #include "vq_tc.cuh"
 
@@ -85,9 +78,6 @@ __device__ __forceinline__ float key_value(unsigned long long key) { return ord_
 constexpr uint32_t kOrdNegInf = 0x007FFFFFu;                       // orderable(-inf)
 constexpr unsigned long long kKeyNegInf = 0x007FFFFFull << 32;     // (-inf, no code)
 
-constexpr int kQueueSlots = 128;  // per epilogue warp (ring): <= 31 left over + 64 pushed between two drain checks
-constexpr int kQueueWords = 10;   // 8 scores (q_sc) + group id, row | hi16 << 16 (q_meta)
-
 struct TcParams {
     const void* z;
     int64_t z_row_stride;
@@ -102,37 +92,11 @@ struct TcParams {
     int64_t row_offset;
     unsigned long long* keys; // (N) merged with atomicMax
     float* second;            // (N) deterministic modes: runner-up approximate score (orderable bits, atomicMax)
-    int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies, 64 = no events
-    unsigned int* n_events;   // nullable: += groups expanded by the sampler (statistics)
+    int debug;                // tuning aid (B200VQ_TC_DEBUG): 1 = no MMA, 2 = no epilogue work, 4 = no tile copies
+    unsigned int* n_events;   // unused (kept for layout compatibility of the tuning tools)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
-
-// ---- stochastic: expand up to 32 queued groups, one per lane (the 8 Gumbels of the group), and merge
-// each one's best perturbed score into its row's key ---------------------------------------------------
-__device__ __noinline__ void sample_flush(const float* q_sc, const uint2* q_meta, uint32_t qhead, uint32_t n, uint32_t lane,
-                                          unsigned long long* s_key, uint32_t grow0, float t_inv, uint64_t seed,
-                                          uint64_t offset, uint32_t k_end_global) {
-    if (lane < n) {
-        const uint32_t slot = (qhead + lane) & (kQueueSlots - 1);
-        const float4 s0 = *reinterpret_cast<const float4*>(q_sc + slot * 8);
-        const float4 s1 = *reinterpret_cast<const float4*>(q_sc + slot * 8 + 4);
-        const uint2 meta = q_meta[slot];
-        const uint32_t group = meta.x, rl = meta.y & 0xFFu, hi16 = meta.y >> 16;
-        float g[8];
-        group_noise(group, grow0 + rl, seed, offset, hi16, g);
-        const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-        float bv = -INFINITY;
-        uint32_t bk = group * 8;
-#pragma unroll
-        for (int p = 0; p < 8; ++p) {
-            const float v = fmaf(s[p], t_inv, g[p]);
-            if (group * 8 + p < k_end_global && v > bv) { bv = v; bk = group * 8 + p; }
-        }
-        atomicMax(s_key + rl, make_key(bv, bk));
-    }
-    __syncwarp();
-}
 
 __device__ __forceinline__ float lg2_approx(float x) {
     float y;
@@ -151,7 +115,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
     return 1024 /*align slack*/ + static_cast<size_t>(kTcRows) * tc_a_chunks(D) * 16 + kTcStages * tc_tile_bytes(D) +
-           kTcEpiWarps * kQueueSlots * kQueueWords * 4 + kTcRows * 8 + 2 * kTcRows * 4 + 512;
+           kTcRows * 8 + 2 * kTcRows * 4 + 512;
 }
 
 template <int D, typename T, int MODE>
@@ -160,19 +124,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     constexpr uint32_t A_BYTES = kTcRows * tc_a_chunks(D) * 16;
     constexpr uint32_t B_BYTES = static_cast<uint32_t>(tc_tile_bytes(D));
     constexpr uint32_t A_LBO = kTcRows * 16, B_LBO = kTcCodes * 16, SBO = 128;
-    constexpr bool SAMPLE = MODE == B200VQ_MODE_SAMPLE;
+    static_assert(MODE != B200VQ_MODE_SAMPLE, "stochastic mode: tc_sample_kernel (vq_tc_sample.cuh)");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sA = smem;
     uint8_t* sB = sA + A_BYTES;
-    float* s_queue = reinterpret_cast<float*>(sB + kTcStages * B_BYTES);
-    unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_queue + kTcEpiWarps * kQueueSlots * kQueueWords);
+    unsigned long long* s_key = reinterpret_cast<unsigned long long*>(sB + kTcStages * B_BYTES);
     uint32_t* s_second = reinterpret_cast<uint32_t*>(s_key + kTcRows);
     uint32_t* s_thr = s_second + kTcRows;
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_thr + kTcRows);  // full[S], empty[S], tfull[2], tempty[2]
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2 * kTcStages + 2 * kTcBufs);
-    uint32_t* s_qtail = s_tmem + 4;   // (kTcEpiWarps) queue tails of the sampling epilogue
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kTcRows;
@@ -204,7 +166,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
         s_key[threadIdx.x] = make_key(-INFINITY, first_code);
         s_second[threadIdx.x] = kOrdNegInf;
         s_thr[threadIdx.x] = kOrdNegInf;
-        if (threadIdx.x < kTcEpiWarps) s_qtail[threadIdx.x] = 0u;
     } else if (warp == kTcEpiWarps) {
         if (lane == 0) {
             for (int s = 0; s < kTcStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -257,7 +218,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
     } else {
         // ===== epilogue groups: group g = warps 4g..4g+3, columns [128*(g&1), +128) of buffer g>>1 ==========
         const int grp = warp >> 2, buf = grp >> 1, half = grp & 1;
-        if constexpr (!SAMPLE) {
+        {
             // ---- deterministic modes: branch-free chunk tracking, two register buffers in flight ----------
             const uint32_t row_local = 32 * (warp & 3) + lane;
             const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
@@ -307,127 +268,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_scores_kernel(const TcParams
                     atomicMax(reinterpret_cast<unsigned int*>(p.second) + row, orderable(runner));
                 }
             }
-        } else {
-        // ---- stochastic mode: lazy Gumbel-max.  Per group of 8 codes a few branch-free instructions decide
-        // whether the group's bound (its largest score + the largest Gumbel its 16 head bits allow) can beat
-        // the row's best perturbed score so far.  Such groups are rare after the first tiles and rows of a
-        // warp hit them at different times, so a lane only QUEUES them (8 scores + ids into the warp's
-        // shared-memory ring, slot from a shared-memory atomic); whenever 32 are waiting the warp expands
-        // them one per lane with all lanes busy (sample_flush).
-        const uint32_t row_local = 32 * (warp & 3) + lane;
-        float* q_sc = s_queue + warp * (kQueueSlots * kQueueWords);
-        uint2* q_meta = reinterpret_cast<uint2*>(q_sc + kQueueSlots * 8);
-        uint32_t qhead = 0, qtail = 0;   // ring positions, warp-uniform
-        const uint32_t lt_mask = (1u << lane) - 1u;
-        const uint32_t flush_min = (p.debug >> 8) & 0xFF ? (p.debug >> 8) & 0xFF : 32u;   // tuning: smallest batch drained at a tile end
-        const uint32_t grow0 = static_cast<uint32_t>(p.row_offset + row0);
-        const uint32_t k_end_global = static_cast<uint32_t>(p.k_offset + p.K);
-        const uint32_t t_lane = tmem_base + ((32u * (warp & 3)) << 16) + buf * kTcCodes + half * 128;
-        const float tl2e = p.t_inv * kLog2e;
-        float thr = INFINITY;   // 19.02 - vstar * log2(e); "everything can matter" until a key exists
-        uint32_t va[32];
-        float lh[16];           // log2 of the tile's 16 group heads
-        uint32_t group0 = 0;
-        // one chunk of 32 columns: 4 group tests, queue the candidates, drain when 32 are waiting
-        auto process = [&](uint32_t (&v)[32], const int ch, const int valid) {
-            thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);   // all four epilogue groups' progress
-            if ((ch + 1) * 32 > valid) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (ch * 32 + j >= valid) v[j] = 0xFF800000u;
-            }
-            uint32_t evmask = 0;
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                evmask |= fmaf(max8(&v[8 * g]), tl2e, thr) > lh[4 * ch + g] ? (1u << g) : 0u;
-            }
-            if (__any_sync(0xffffffffu, evmask != 0u) && !(p.debug & 64)) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    // ring slots from a ballot: the tail lives in a (warp-uniform) register, no shared-memory atomic,
-                    // and a group none of the 32 rows cares about costs one VOTE
-                    const uint32_t m = __ballot_sync(0xffffffffu, (evmask >> g) & 1u);
-                    if (m != 0u) {
-                        if ((evmask >> g) & 1u) {
-                            const uint32_t slot = (qtail + __popc(m & lt_mask)) & (kQueueSlots - 1);
-                            float* e = q_sc + slot * 8;
-                            *reinterpret_cast<uint4*>(e) = make_uint4(v[8 * g], v[8 * g + 1], v[8 * g + 2], v[8 * g + 3]);
-                            *reinterpret_cast<uint4*>(e + 4) = make_uint4(v[8 * g + 4], v[8 * g + 5], v[8 * g + 6], v[8 * g + 7]);
-                            // the head back from its log2 (exact: |2^lg2(h) - h| << 0.5 for h < 2^16)
-                            q_meta[slot] = make_uint2(group0 + 4 * ch + g,
-                                                      row_local | (__float2uint_rn(ex2_approx(lh[4 * ch + g])) << 16));
-                        }
-                        qtail += __popc(m);
-                    }
-                    if (g & 1) {
-                        // Drain inside the tile only when the ring could overflow (the next two groups add <= 64):
-                        // while this warp expands groups its half of the accumulator is not released and the
-                        // MMAs of the buffer wait.  The regular drain is at the end of the tile, after the release.
-                        uint32_t pending = qtail - qhead;
-                        if (pending > kQueueSlots - 64u) {
-                            __syncwarp();
-                            do {
-                                sample_flush(q_sc, q_meta, qhead, 32u, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
-                                qhead += 32u;
-                                pending -= 32u;
-                            } while (pending >= 32u);
-                            thr = fmaf(key_value(s_key[row_local]), -kLog2e, 19.02f);
-                        }
-                    }
-                }
-            }
-        };
-        for (int i = buf; i < ntiles; i += kTcBufs) {
-            const int64_t code0 = static_cast<int64_t>(tile_begin + i) * kTcCodes + half * 128;  // index within the image
-            group0 = static_cast<uint32_t>((p.k_offset + code0) >> 3);                           // multiple of 16
-            const int valid = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(128), p.K - code0)));
-            // Before the accumulator is needed: 16 random bits per group (two Philox calls per tile) and
-            // their log2, so that the in-loop test   head < 2^(m * tl2e + thr)   is   m * tl2e + thr > log2(head)
-            // (one FFMA + one compare); head 0 -> -inf: always a candidate.
-            {
-                const Philox4 r0 = group_head_words(group0 >> 3, grow0 + row_local, p.seed, p.offset);
-                const Philox4 r1 = group_head_words((group0 >> 3) + 1, grow0 + row_local, p.seed, p.offset);
-#pragma unroll
-                for (int g = 0; g < 16; ++g)
-                    lh[g] = lg2_approx(__uint_as_float(0x4B000000u | head_hi16(g < 8 ? r0 : r1, g & 7)) - 8388608.0f);
-            }
-            mbar_wait(bar_tfull + 8 * buf, (i / kTcBufs) & 1);
-            tc_fence_after();
-            if (half == 0 && (warp & 3) == 0 && lane == 0) mbar_arrive(bar_empty + 8 * (i % kTcStages));  // MMAs have read the stage
-            if (p.debug & 2) { tc_fence_before(); mbar_arrive(bar_tempty + 8 * buf); continue; }
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-                tmem_ld32(t_lane + ch * 32, va);
-                tmem_ld_wait32(va);
-                if (ch == 3) {   // this group's half of the buffer is in registers: hand it back to the MMA warp
-                    tc_fence_before();
-                    mbar_arrive(bar_tempty + 8 * buf);
-                }
-                process(va, ch, valid);
-            }
-            // regular drain, off the accumulator's critical path
-            __syncwarp();
-            for (uint32_t pending = qtail - qhead; pending >= flush_min;) {
-                const uint32_t n = min(32u, pending);
-                sample_flush(q_sc, q_meta, qhead, n, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
-                qhead += n;
-                pending -= n;
-            }
         }
-        __syncwarp();
-        for (uint32_t pending = qtail - qhead; pending != 0u;) {
-            const uint32_t n = min(32u, pending);
-            sample_flush(q_sc, q_meta, qhead, n, lane, s_key, grow0, p.t_inv, p.seed, p.offset, k_end_global);
-            qhead += n;
-            pending -= n;
-        }
-        if (p.n_events && lane == 0) atomicAdd(p.n_events, qhead);
-        // all four groups done -> publish the rows (named barrier over the 512 epilogue threads)
-        asm volatile("bar.sync 1, 512;" ::: "memory");
-        if (grp == 0) {
-            const int64_t row = row0 + row_local;
-            if (row < p.N && ntiles > 0) atomicMax(p.keys + row, s_key[row_local]);
-        }
-        }  // SAMPLE
     }
     // ---- teardown ------------------------------------------------------------------------------------
     tc_fence_before();
