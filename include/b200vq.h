@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 120
+#define B200VQ_VERSION 121
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -47,6 +47,7 @@ extern "C" {
 #define B200VQ_EALIGN (-3)    /* pointer or stride not aligned as required     */
 #define B200VQ_ECUDA (-4)     /* a CUDA call failed; see b200vq_last_cuda_error */
 #define B200VQ_EWORKSPACE (-5) /* workspace too small / null                    */
+#define B200VQ_ENOALLOC_SIZE (-6) /* (C, D) needs more than B200VQ_NOALLOC_SCRATCH_BYTES of built-in scratch */
 
 typedef void* b200vq_stream_t; /* cudaStream_t */
 
@@ -269,6 +270,25 @@ size_t b200vq_weight_grad_workspace_bytes(int C, int D);
 int b200vq_weight_grad_ws(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
                           int dw_is_dc, float* colsum, void* workspace, size_t workspace_bytes,
                           b200vq_stream_t stream);
+/*
+ * b200vq_weight_grad_noalloc -- b200vq_weight_grad_ws without a workspace argument and without any allocation.
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *   - same arguments, kernels, path selection and results as b200vq_weight_grad_ws; the per-CTA slabs live in a
+ *     static device array of B200VQ_NOALLOC_SCRATCH_BYTES (24 MiB) inside the library, held by every GPU that
+ *     loads it until the process exits.  The call makes no cudaMalloc / cudaFree / allocating library call.
+ *   - (C, D) with b200vq_weight_grad_workspace_bytes(C, D) above that limit (e.g. C = 1024 with D >= 24 on a
+ *     148-SM part) are refused with B200VQ_ENOALLOC_SIZE; N is not limited.
+ *   - every call on a device shares the one array: calls that overlap on the GPU (different streams, or graphs
+ *     replayed concurrently) race on it -- keep them on one stream or order them with events.  The array keeps
+ *     the previous call's slabs; nothing has to start at zero, because each slab the reduction reads is written
+ *     in full by its CTA in the same call.
+ *   - the array's device address is resolved with cudaGetSymbolAddress on the first call per device (with the
+ *     caller's device current) and cached; make that first call outside stream capture.
+ */
+#define B200VQ_NOALLOC_SCRATCH_BYTES (24u << 20)
+int b200vq_weight_grad_noalloc(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
+                               int dw_is_dc, float* colsum, b200vq_stream_t stream);
 /*
  * Backward of out_linear in ONE pass over grad_output g (N,C; row stride ldg), instead of
  * b200vq_linear_in (grad of the input) + b200vq_weight_grad_ws (weight / bias grads) reading it twice:

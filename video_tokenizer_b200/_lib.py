@@ -61,6 +61,7 @@ SIGNATURES = {
     "b200vq_grad_out": (_i32, [_vp, _i64, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b200vq_weight_grad_workspace_bytes": (_sz, [_i32, _i32]),
     "b200vq_weight_grad_ws": (_i32, [_vp, _i64, _vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp, _sz, _vp]),
+    "b200vq_weight_grad_noalloc": (_i32, [_vp, _i64, _vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp]),
     "b200vq_colsum": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "b200vq_gather_owned": (_i32, [_vp, _i64, _vp, _i64, _i64, _i32, _vp, _vp]),
     "b200vq_bottleneck_workspace_bytes": (_sz, [_i64, _i32, _i32, _i64]),
@@ -101,7 +102,7 @@ def load(build_if_missing: bool = True):
             except AttributeError as e:
                 raise B200VQError(f"{path} does not export {name}") from e
             fn.restype, fn.argtypes = res, args
-        if lib.b200vq_version() < 120:
+        if lib.b200vq_version() < 121:
             raise B200VQError("libb200vq.so is older than this Python package")
         _lib = lib
         return lib

@@ -57,6 +57,7 @@ const char* b200vq_error_string(int code) {
         case B200VQ_EALIGN: return "pointer or offset not aligned as required";
         case B200VQ_ECUDA: return "CUDA error (see b200vq_last_cuda_error)";
         case B200VQ_EWORKSPACE: return "workspace null or too small";
+        case B200VQ_ENOALLOC_SIZE: return "size exceeds the library's built-in scratch (B200VQ_NOALLOC_SCRATCH_BYTES); use the workspace variant";
         default: return "unknown error";
     }
 }

@@ -298,6 +298,48 @@ int b200vq_weight_grad_ws(const float* x, int64_t ldx, const float* y, int64_t N
                               static_cast<cudaStream_t>(stream));
 }
 
+}  // extern "C"
+
+// ---- allocation-free variant of b200vq_weight_grad_ws ---------------------------------------------------------
+// The per-CTA slabs live in a file-scope device array instead of a caller workspace: nothing is allocated by the
+// call, so it can be used where cudaMalloc is forbidden (stream capture, serving loops).  Every GPU that loads the
+// library holds B200VQ_NOALLOC_SCRATCH_BYTES until the process exits.  In host code `g_noalloc_scratch` is only a
+// handle of the symbol, never a device address: its address on the current device comes from cudaGetSymbolAddress,
+// looked up once per device and cached.
+namespace {
+__device__ __align__(256) float g_noalloc_scratch[B200VQ_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+int noalloc_scratch(float** out) {
+    static std::atomic<float*> cached[64];
+    const int dev = current_device();   // the lookup is made with the caller's device current
+    float* p = dev < 64 ? cached[dev].load(std::memory_order_acquire) : nullptr;
+    if (!p) {
+        void* sym = nullptr;
+        if (int rc = cuda_check(cudaGetSymbolAddress(&sym, g_noalloc_scratch))) return rc;
+        if (!sym) return B200VQ_ECUDA;
+        p = static_cast<float*>(sym);
+        if (dev < 64) cached[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return B200VQ_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int b200vq_weight_grad_noalloc(const float* x, int64_t ldx, const float* y, int64_t N, int C, int D, float* dw,
+                               int dw_is_dc, float* colsum, b200vq_stream_t stream) {
+    if (N < 0) return B200VQ_EINVAL;
+    if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
+    // same slab layout as b200vq_weight_grad_ws; (C, D) whose slabs do not fit the built-in array are refused
+    if (b200vq_weight_grad_workspace_bytes(C, D) > static_cast<size_t>(B200VQ_NOALLOC_SCRATCH_BYTES)) return B200VQ_ENOALLOC_SIZE;
+    float* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    // nothing to clear: every slab that the reduction reads is written in full by its CTA in the same call, and the
+    // paths that accumulate with atomics instead zero dw / colsum (caller memory) themselves
+    return launch_weight_grad(x, ldx, y, N, C, D, dw, dw_is_dc, colsum, scratch, static_cast<cudaStream_t>(stream));
+}
+
 int b200vq_colsum(const float* y, int64_t N, int D, float* out, b200vq_stream_t stream) {
     if (N < 0 || D <= 0 || D > 32 || !out) return B200VQ_EINVAL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
