@@ -350,6 +350,79 @@ __global__ void __launch_bounds__(128) input_norms_kernel(const float* __restric
         atomicAdd(out2 + threadIdx.x, sqrtf(t) / static_cast<float>(B));
     }
 }
+// ---- side lane: independent small kernels of the one-call step run beside the big streaming passes ------------
+// One non-blocking stream + a few events per device, created on the first call that is not under stream capture and
+// kept for the life of the process.  fork() makes the lane wait for everything enqueued on the caller's stream so
+// far, join() makes the caller's stream wait for the lane; both are plain event record / wait, so the calls stay
+// asynchronous and capturable (the lane joins a CUDA-graph capture through the event and leaves it at join()).
+// B200VQ_NO_OVERLAP=1 keeps everything on the caller's stream.
+struct SideLane {
+    std::atomic<int> state{0};   // 0 = not tried, 1 = ready, -1 = unavailable
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+SideLane g_side[64];
+std::mutex g_side_mu;
+
+// Which forks are used: bit 1 codebook preparation beside in_linear, 2 usage statistics beside out_linear, 4 backward
+// tail (codebook Jacobian, bias gradient, grad_W_in) beside grad_x, 8 grad_W_in stays on the caller's stream.
+// The streaming kernels run one persistent CTA per SM, so a side kernel that takes an SM stretches them when both
+// really start together, which is what a replayed graph does: under capture only the forks that pay there are used
+// (measured, profiles/r02_summary.md: 13 -> 0.554 ms against 0.569-0.576 serial; eager 7 -> 0.570 against 0.604).
+// B200VQ_OVERLAP overrides both.
+// Outside a capture every fork costs a few host microseconds of event calls: small batches (host-bound) stay serial.
+inline int overlap_mask(cudaStream_t st, int64_t N) {
+    static const int forced = [] { const char* e = std::getenv("B200VQ_OVERLAP"); return e ? std::atoi(e) : -1; }();
+    if (forced >= 0) return forced;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cs != cudaStreamCaptureStatusNone) return 13;
+    return N >= 32768 ? 7 : 0;
+}
+SideLane* side_lane(cudaStream_t st) {
+    static const bool off = std::getenv("B200VQ_NO_OVERLAP") != nullptr;
+    const int dev = current_device();
+    if (off || dev >= 64) return nullptr;
+    SideLane& s = g_side[dev];
+    const int state = s.state.load(std::memory_order_acquire);
+    if (state == 1) return &s;
+    if (state < 0) return nullptr;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cs != cudaStreamCaptureStatusNone) return nullptr;   // never create objects inside a capture: this call runs serially
+    std::lock_guard<std::mutex> lock(g_side_mu);
+    if (s.state.load(std::memory_order_acquire) == 1) return &s;
+    bool ok = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < 4; ++i) ok = cudaEventCreateWithFlags(&s.ev[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+    s.state.store(ok ? 1 : -1, std::memory_order_release);
+    return ok ? &s : nullptr;
+}
+// every early return between fork() and join() still joins (destructor), so a capture is never left forked
+struct SideScope {
+    SideLane* lane;
+    cudaStream_t main;
+    int ev_join;
+    bool forked = false;
+    SideScope(SideLane* l, cudaStream_t m, int ev_fork, int ev_join_) : lane(l), main(m), ev_join(ev_join_) {
+        if (!lane) return;
+        std::lock_guard<std::mutex> lock(g_side_mu);   // record + wait as one step: another thread may use the same lane
+        if (cudaEventRecord(lane->ev[ev_fork], main) == cudaSuccess && cudaStreamWaitEvent(lane->stream, lane->ev[ev_fork], 0) == cudaSuccess)
+            forked = true;
+        else { cudaGetLastError(); lane = nullptr; }
+    }
+    cudaStream_t side() const { return forked ? lane->stream : main; }
+    int join() {
+        if (!forked) return B200VQ_OK;
+        forked = false;
+        std::lock_guard<std::mutex> lock(g_side_mu);
+        int rc = cuda_check(cudaEventRecord(lane->ev[ev_join], lane->stream));
+        if (!rc) rc = cuda_check(cudaStreamWaitEvent(main, lane->ev[ev_join], 0));
+        return rc;
+    }
+    ~SideScope() { join(); }
+};
+
 struct BnLayout {
     size_t e2, image, vq, ga, gz, gemb, wg, total;
 };
@@ -394,26 +467,37 @@ int b200vq_bottleneck_forward(const float* x, int64_t ldx, int64_t N, int C, con
     char* ws = static_cast<char*>(workspace);
     float* e2 = reinterpret_cast<float*>(ws + l.e2);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, act_dtype, true, st);
-    if (rc) return rc;
-    if (norms2) {
-        if (n_first <= 0 || N % n_first) return B200VQ_EINVAL;
-        if ((rc = cuda_check(cudaMemsetAsync(norms2, 0, 2 * sizeof(float), st)))) return rc;
-        input_norms_kernel<<<static_cast<unsigned>(N / n_first), 128, 0, st>>>(x, ldx, n_first, C, N / n_first, norms2);
-        if ((rc = launch_check())) return rc;
-    }
-    if ((rc = b200vq_prepare_codebook(weight, K, D, l2norm, emb, e2, wnorm, stream))) return rc;
+    if (norms2 && (n_first <= 0 || N % n_first)) return B200VQ_EINVAL;
+    SideLane* lane = side_lane(st);
+    const int forks = overlap_mask(st, N);
+    int rc = B200VQ_OK;
     void* image = nullptr;
-    if (use_tc && b200vq_tc_supported(D, l2norm, mode)) {
-        image = ws + l.image;
-        if ((rc = b200vq_prepare_codebook_tc(emb, K, D, image, stream))) return rc;
+    {
+        // codebook preparation and the input-norm diagnostics do not depend on the latents: beside in_linear
+        SideScope sc((forks & 1) ? lane : nullptr, st, 0, 1);
+        cudaStream_t s2 = sc.side();
+        if (norms2) {
+            if ((rc = cuda_check(cudaMemsetAsync(norms2, 0, 2 * sizeof(float), s2)))) return rc;
+            input_norms_kernel<<<static_cast<unsigned>(N / n_first), 128, 0, s2>>>(x, ldx, n_first, C, N / n_first, norms2);
+            if ((rc = launch_check())) return rc;
+        }
+        if ((rc = b200vq_prepare_codebook(weight, K, D, l2norm, emb, e2, wnorm, s2))) return rc;
+        if (use_tc && b200vq_tc_supported(D, l2norm, mode)) {
+            image = ws + l.image;
+            if ((rc = b200vq_prepare_codebook_tc(emb, K, D, image, s2))) return rc;
+        }
+        if ((rc = launch_linear_in(x, ldx, N, C, w_in, 0, b_in, D, z, act_dtype, true, st))) return rc;
+        if ((rc = sc.join())) return rc;
     }
     rc = forward_impl(z, act_dtype, D, N, D, emb, e2, image, K, mode, l2norm, t_inv, seed, offset,
                       reinterpret_cast<unsigned long long*>(philox_dev), n_first, beta, w_cb, znorm, ste, idx, zlen, hist,
                       hist_first, losses, ws + l.vq, b200vq_workspace_bytes(N, D, K), st);
     if (rc) return rc;
-    if (usage4 && (rc = b200vq_usage_stats(hist_first, hist, K, usage4, stream))) return rc;
-    return launch_linear_out(ste, N, D, w_out, 0, b_out, C, out, act_dtype, ldo, nullptr, 0, 0, add, add_rows, nullptr, st);
+    // the usage statistics (one CTA, latency-bound) beside out_linear
+    SideScope sc(usage4 && (forks & 2) ? lane : nullptr, st, 2, 3);
+    if (usage4 && (rc = b200vq_usage_stats(hist_first, hist, K, usage4, sc.side()))) return rc;
+    if ((rc = launch_linear_out(ste, N, D, w_out, 0, b_out, C, out, act_dtype, ldo, nullptr, 0, 0, add, add_rows, nullptr, st))) return rc;
+    return sc.join();
 }
 
 int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, const float* g_losses, const float* g_ste,
@@ -459,12 +543,17 @@ int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, co
     if ((rc = b200vq_backward(ga_in, g_znorm, g_losses, znorm, zlen, idx, emb, nullptr, 0, N, D, K, l2norm, N, beta, w_cb, gz,
                               B200VQ_DT_F32, gemb, stream)))
         return rc;
-    if (grad_weight && (rc = b200vq_codebook_backward(gemb, g_emb, emb, wnorm, K, D, l2norm, grad_weight, stream))) return rc;
     if (g_z && (rc = add_inplace(gz, g_z, N * D, st))) return rc;
+    // grad_x (one pass of stores) on the caller's stream; the codebook Jacobian, the bias gradient and grad_W_in (one
+    // pass of loads over x) beside it
+    const int forks = overlap_mask(st, N);
+    SideScope sc(grad_x && (forks & 4) ? side_lane(st) : nullptr, st, 0, 1);
+    cudaStream_t s2 = sc.side();
+    if (grad_weight && (rc = b200vq_codebook_backward(gemb, g_emb, emb, wnorm, K, D, l2norm, grad_weight, s2))) return rc;
+    if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, s2))) return rc;
+    if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, (forks & 8) ? st : s2))) return rc;
     if (grad_x && (rc = b200vq_linear_out(gz, N, D, w_in, 1, nullptr, C, grad_x, ldgx, stream))) return rc;
-    if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, st))) return rc;
-    if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, stream))) return rc;
-    return B200VQ_OK;
+    return sc.join();
 }
 
 }  // extern "C"
