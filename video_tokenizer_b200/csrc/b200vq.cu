@@ -197,13 +197,10 @@ int forward_impl(const void* z, int z_dtype, int64_t z_row_stride, int64_t N, in
     double* scratch = reinterpret_cast<double*>(static_cast<char*>(workspace) + align_up(static_cast<size_t>(N) * 8));
     const bool tc = image && b200vq_tc_supported(D, l2norm, mode);
     int rc;
-    // histograms: one fill when the two are adjacent (the (2, K) tensor of the one-call path)
-    if (hist && hist_first && hist_first == hist + K) {
-        if ((rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 8, st)))) return rc;
-    } else {
-        if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
-        if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
-    }
+    // one fill per histogram, always: two buffers that happen to be adjacent in the address space may still be two
+    // allocations, and a memset that spans two allocations is an invalid argument (seen with the torch allocator)
+    if (hist && (rc = cuda_check(cudaMemsetAsync(hist, 0, static_cast<size_t>(K) * 4, st)))) return rc;
+    if (hist_first && (rc = cuda_check(cudaMemsetAsync(hist_first, 0, static_cast<size_t>(K) * 4, st)))) return rc;
     if (tc && mode == B200VQ_MODE_SAMPLE) {
         // keys + sums are zeroed; the deterministic modes' scratch is not needed
         if ((rc = cuda_check(cudaMemsetAsync(workspace, 0, align_up(static_cast<size_t>(N) * 8) + align_up(2 * sizeof(double)), st))))

@@ -18,13 +18,24 @@ namespace host {
 extern thread_local int g_last_cuda_error;            // b200vq.cu
 extern std::atomic<unsigned long long> g_launches;    // b200vq.cu
 
-inline int cuda_check(cudaError_t e) {
+// B200VQ_TRACE=1: every failing CUDA call / launch is reported on stderr with its source location
+inline bool trace_enabled() {
+    static const bool on = std::getenv("B200VQ_TRACE") != nullptr;
+    return on;
+}
+inline int cuda_check_at(cudaError_t e, const char* file, int line) {
     if (e == cudaSuccess) return B200VQ_OK;
     g_last_cuda_error = static_cast<int>(e);
+    if (trace_enabled()) std::fprintf(stderr, "[b200vq] %s:%d: %s (%d)\n", file, line, cudaGetErrorString(e), static_cast<int>(e));
     cudaGetLastError();  // clear the sticky launch error so later calls can proceed
     return B200VQ_ECUDA;
 }
-inline int launch_check() { g_launches.fetch_add(1, std::memory_order_relaxed); return cuda_check(cudaPeekAtLastError()); }
+inline int launch_check_at(const char* file, int line) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return cuda_check_at(cudaPeekAtLastError(), file, line);
+}
+#define cuda_check(e) cuda_check_at((e), __FILE__, __LINE__)
+#define launch_check() launch_check_at(__FILE__, __LINE__)
 
 inline int current_device() {
     int dev = 0;
