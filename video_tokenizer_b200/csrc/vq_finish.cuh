@@ -200,27 +200,36 @@ __global__ void __launch_bounds__(256) decode_kernel(const int64_t* __restrict__
 // Trainer usage statistics (larp_tokenizer_trainer.py:335-352).  Single block of 1024.
 __global__ void __launch_bounds__(1024) usage_stats_kernel(const int32_t* __restrict__ hf, const int32_t* __restrict__ hb,
                                                            int64_t K, float* __restrict__ out4) {
-    __shared__ double s_red[32];
-    __shared__ double s_bcast;
-    auto block_sum = [&](double v) -> double {
-        v = warp_sum_d(v);
-        __syncthreads();
-        if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            double t = s_red[threadIdx.x];
-            t = warp_sum_d(t);
-            if (threadIdx.x == 0) s_bcast = t;
+    // two block reductions (counts, then the two entropies), each over a small vector so that the barriers are shared
+    __shared__ double s_red[3][32];
+    __shared__ double s_bcast[3];
+    auto block_sum3 = [&](double (&v)[3]) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[i] = warp_sum_d(v[i]);
+        __syncthreads();   // s_red / s_bcast of the previous reduction are no longer read
+        if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i) s_red[i][threadIdx.x >> 5] = v[i];
         }
         __syncthreads();
-        return s_bcast;
+        if (threadIdx.x < 96) {
+            const double t = warp_sum_d(s_red[threadIdx.x >> 5][threadIdx.x & 31]);
+            if ((threadIdx.x & 31) == 0) s_bcast[threadIdx.x >> 5] = t;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[i] = s_bcast[i];
     };
-    double nzf = 0, nzb = 0, tot = 0;
+    // counts are exact in int32 (<= N < 2^31 per bin, K bins per thread-stride); the sums go through double
+    int nzf_i = 0, nzb_i = 0;
+    long long tot_i = 0;
     for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
         const int cf = hf[k], cb = hb[k];
-        nzf += cf > 0; nzb += cb > 0; tot += cf;
+        nzf_i += cf > 0; nzb_i += cb > 0; tot_i += cf;
     }
-    nzf = block_sum(nzf); nzb = block_sum(nzb); tot = block_sum(tot);
+    double c3[3] = {static_cast<double>(nzf_i), static_cast<double>(nzb_i), static_cast<double>(tot_i)};
+    block_sum3(c3);
+    const double nzf = c3[0], nzb = c3[1], tot = c3[2];
     double kl = 0, ent = 0;
     if (tot > 0) {
         const float logK = logf(static_cast<float>(K));
@@ -233,12 +242,13 @@ __global__ void __launch_bounds__(1024) usage_stats_kernel(const int32_t* __rest
             if (cf > 0) kl += static_cast<double>(avg * (logf(avg) + logK));
         }
     }
-    kl = block_sum(kl); ent = block_sum(ent);
+    double e3[3] = {kl, ent, 0.0};
+    block_sum3(e3);
     if (threadIdx.x == 0) {
         out4[0] = static_cast<float>(nzf / static_cast<double>(K));
         out4[1] = static_cast<float>(nzb / static_cast<double>(K));
-        out4[2] = static_cast<float>(kl);
-        out4[3] = static_cast<float>(exp(ent));
+        out4[2] = static_cast<float>(e3[0]);
+        out4[3] = static_cast<float>(exp(e3[1]));
     }
 }
 

@@ -15,6 +15,8 @@ from __future__ import annotations
 
 from typing import Callable, List, Optional, Sequence, Tuple
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -181,6 +183,15 @@ class _CodebookShardedVQ(torch.autograd.Function):
         f32 = dict(dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             emb_l, e2_l, wnorm_l = VF.prepare_codebook(weight_local, l2norm)
+            # Equal shards: gather the normalised slices into a full (K, D) table WHILE the local slice is scored (the
+            # table does not depend on the scores); the winning rows are then read locally and the (N, D) all-reduce of
+            # the owners' rows is not needed.  Unequal shards keep the owner-rows exchange.
+            world = dist.get_world_size(group) if dist.is_initialized() else 1
+            gather_work, emb_full = None, None
+            if world > 1 and K % world == 0 and K_local == K // world and k_begin == dist.get_rank(group) * K_local \
+                    and os.environ.get("B200VQ_SHARDED_ROWS", "gather") == "gather":
+                emb_full = torch.empty(K, D, **f32)
+                gather_work = dist.all_gather_into_tensor(emb_full, emb_l, group=group, async_op=True)
             keys = torch.zeros(N, dtype=torch.int64, device=dev)
             use_tc = VF.SCORING == "tc" and lib.b200vq_tc_supported(D, int(l2norm), mode) and k_begin % 256 == 0
             if use_tc:
@@ -196,10 +207,15 @@ class _CodebookShardedVQ(torch.autograd.Function):
                                                      offset, 0, keys.data_ptr(), st()), "b200vq_scores_partial")
             allreduce_max_keys(keys, group)                                   # the cross-GPU max-loc
             rows = torch.empty(N, D, **f32)
-            _lib.check(lib.b200vq_gather_owned(keys.data_ptr(), N, emb_l.data_ptr(), K_local, k_begin, D, rows.data_ptr(),
-                                               st()), "b200vq_gather_owned")
-            if dist.is_initialized() and dist.get_world_size(group) > 1:
-                dist.all_reduce(rows, op=dist.ReduceOp.SUM, group=group)      # only the owner wrote non-zero
+            if gather_work is not None:
+                gather_work.wait()                                            # the current stream waits for the table
+                _lib.check(lib.b200vq_gather_owned(keys.data_ptr(), N, emb_full.data_ptr(), K, 0, D, rows.data_ptr(), st()),
+                           "b200vq_gather_owned")
+            else:
+                _lib.check(lib.b200vq_gather_owned(keys.data_ptr(), N, emb_l.data_ptr(), K_local, k_begin, D, rows.data_ptr(),
+                                                   st()), "b200vq_gather_owned")
+                if world > 1:
+                    dist.all_reduce(rows, op=dist.ReduceOp.SUM, group=group)  # only the owner wrote non-zero
             znorm = torch.empty(*z.shape, **f32)
             ste = torch.empty(*z.shape, **f32)
             idx = torch.empty(N, dtype=torch.int64, device=dev)
