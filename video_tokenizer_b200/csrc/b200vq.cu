@@ -373,7 +373,7 @@ inline int overlap_mask(cudaStream_t st, int64_t N) {
     if (forced >= 0) return forced;
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return 0; }
-    if (cs != cudaStreamCaptureStatusNone) return 13;
+    if (cs != cudaStreamCaptureStatusNone) return N >= 32768 ? 13 : 7;   // small grids leave SMs free: every fork pays
     return N >= 32768 ? 7 : 0;
 }
 SideLane* side_lane(cudaStream_t st) {

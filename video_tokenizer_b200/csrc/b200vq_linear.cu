@@ -27,13 +27,29 @@ int launch_linear_in(const float* x, int64_t ldx, int64_t N, int C, const float*
     if ((ldx & 3) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w) & 15) ||
         (reinterpret_cast<uintptr_t>(y) & 7))
         return B200VQ_EALIGN;
-    const size_t smem = static_cast<size_t>(D) * (C + 16) * 4;
-    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + kLinInRows - 1) / kLinInRows, static_cast<int64_t>(sm_count())));
+    const size_t w_smem = static_cast<size_t>(D) * (C + 16) * 4;
+    static const bool no_ring = std::getenv("B200VQ_LIN_IN_NO_RING") != nullptr;   // tuning aid
+    const bool ring = !no_ring && w_smem + lin_in_ring_bytes() <= 227 * 1024;
+    const size_t smem = w_smem + (ring ? lin_in_ring_bytes() : 0);
+    // small batches: split the columns over the warps of a CTA until the grid covers most of the SMs
+    int ksplit = 1;
+    if (ring) {
+        static const int forced = [] { const char* e = std::getenv("B200VQ_LIN_IN_KSPLIT"); return e ? std::atoi(e) : 0; }();   // tuning aid
+        while (ksplit < 8 && ((C / 16) % (2 * ksplit)) == 0 && (N + kLinInRows / ksplit - 1) / (kLinInRows / ksplit) < 3 * sm_count() / 4) ksplit *= 2;
+        if ((forced == 1 || forced == 2 || forced == 4 || forced == 8) && ((C / 16) % forced) == 0) ksplit = forced;
+    }
+    const int64_t rpc = kLinInRows / ksplit;
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((N + rpc - 1) / rpc, static_cast<int64_t>(sm_count())));
     int rc = B200VQ_OK;
 #define B200VQ_LIN_IN_T(DD, PP, OT)                                                              \
     {                                                                                            \
-        if ((rc = set_smem(linear_in_kernel<DD, PP, OT>, smem))) return rc;                      \
-        linear_in_kernel<DD, PP, OT><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, static_cast<OT*>(y)); \
+        if (ring) {                                                                              \
+            if ((rc = set_smem(linear_in_kernel<DD, PP, OT, true>, smem))) return rc;            \
+            linear_in_kernel<DD, PP, OT, true><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, static_cast<OT*>(y), ksplit); \
+        } else {                                                                                 \
+            if ((rc = set_smem(linear_in_kernel<DD, PP, OT>, smem))) return rc;                  \
+            linear_in_kernel<DD, PP, OT><<<blocks, kLinInThreads, smem, st>>>(x, ldx, N, C, w, w_is_cd, bias, static_cast<OT*>(y)); \
+        }                                                                                        \
     }
     // fp32 output: 3xTF32 when `precise` (the latents decide the code indices); the 2-byte outputs of an autocast
     // region carry 8 / 11 significant bits, so one TF32 pass (11 bits in, fp32 accumulate) is already finer than them

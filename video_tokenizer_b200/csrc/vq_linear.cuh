@@ -97,10 +97,22 @@ __device__ __forceinline__ void store4_cs(__half* p, float a, float b, float c, 
 constexpr int kLinInThreads = 512;                      // 16 warps share one staged weight matrix (1 CTA / SM)
 constexpr int kLinInRows = kLinInThreads;               // linear_in: 32 rows per warp (two m16 tiles share every w fragment)
 
-template <int D, bool PRECISE, typename OT = float>
+constexpr int kLinInRing = 4;   // RING: 16-column chunks in flight per row (thread-private cp.async slots in shared memory)
+__host__ __device__ constexpr size_t lin_in_ring_bytes() { return static_cast<size_t>(kLinInRing) * 4 * kLinInThreads * 16; }
+
+// RING = false: the next two chunks of a row wait in registers (8 x 16 bytes in flight per thread).  RING = true: a
+// thread's next four chunks are in flight as cp.async into its own shared-memory slots (16 x 16 bytes per thread,
+// 128 KB per SM) -- the kernel is bound by bytes in flight (one 512-row tile per CTA at 65 536 tokens: 24 dependent
+// round trips per warp with two chunks in flight), not by the tensor pipe.  The slots are private to the thread that
+// fills them, so no barrier is involved; used whenever the ring fits beside the weight matrix.
+template <int D, bool PRECISE, typename OT = float, bool RING = false>
 __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float* __restrict__ x, int64_t ldx, int64_t N, int C,
                                                         const float* __restrict__ w, int w_is_cd,
-                                                        const float* __restrict__ bias, OT* __restrict__ y) {
+                                                        const float* __restrict__ bias, OT* __restrict__ y, int ksplit = 1) {
+    // ksplit (1, 2, 4, 8; RING only): small batches.  A CTA takes 512 / ksplit rows and its 16 warps split the columns
+    // ksplit ways; the partial sums meet in shared memory and are added in a fixed order (deterministic).  A warp's time
+    // is one pass over its columns whatever N is, so without the split 8 192 tokens keep 16 SMs busy for as long as
+    // 65 536 keep 128.
     constexpr int NT = D / 8;
     extern __shared__ float s_w[];  // [D][C + 16]
     const int cs = C + 16;
@@ -117,8 +129,11 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    for (int64_t tile = blockIdx.x; tile * kLinInRows < N; tile += gridDim.x) {   // persistent: w is staged once per CTA
-    const int64_t r0 = tile * kLinInRows + warp * 32 + g;   // rows r0 + 8q, q = 0..3
+    const int rpc = kLinInRows / ksplit;                       // rows per CTA tile
+    const int nrb = (kLinInThreads / 32) / ksplit;             // 32-row blocks per CTA tile
+    const int rb = warp % nrb, sl = warp / nrb;                // this warp: row block, column slice
+    for (int64_t tile = blockIdx.x; tile * rpc < N; tile += gridDim.x) {   // persistent: w is staged once per CTA
+    const int64_t r0 = tile * rpc + rb * 32 + g;   // rows r0 + 8q, q = 0..3
     const float4* xr[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) xr[q] = reinterpret_cast<const float4*>(x + min(r0 + 8 * q, N - 1) * ldx) + t;
@@ -127,18 +142,42 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
     for (int m = 0; m < 2; ++m)
 #pragma unroll
         for (int j = 0; j < NT; ++j) { acc[m][j][0] = acc[m][j][1] = acc[m][j][2] = acc[m][j][3] = 0.f; }
-    const int chunks = C / 16;
-    constexpr int PF = 2;  // chunks in flight per row
+    const int cbeg = sl * ((C / 16) / ksplit), chunks = cbeg + (C / 16) / ksplit;   // this warp's 16-column chunks [cbeg, chunks)
+    constexpr int PF = RING ? 1 : 2;  // register path: chunks in flight per row
     float4 v[PF][4];
+    float4* ring = reinterpret_cast<float4*>(s_w + D * cs) + threadIdx.x;   // slot (stage u, row q): ring[(4 u + q) * 512]
+    if constexpr (RING) {
 #pragma unroll
-    for (int u = 0; u < PF; ++u)
+        for (int u = 0; u < kLinInRing - 1; ++u) {
+            if (cbeg + u < chunks) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) if (u < chunks) v[u][q] = __ldg(xr[q] + 4 * u);
-    for (int c0 = 0; c0 < chunks; c0 += PF) {
+                for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * u + q) * kLinInThreads, xr[q] + 4 * (cbeg + u));
+            }
+            cp_async_commit();
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < PF; ++u)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) if (u < chunks) v[u][q] = __ldg(xr[q] + 4 * u);
+    }
+    for (int c0 = cbeg; c0 < chunks; c0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
             const int c = c0 + u;
             if (c >= chunks) break;
+            if constexpr (RING) {
+                // refill the slot read in the previous iteration, then wait for this iteration's chunk
+                const int nc = c + kLinInRing - 1;
+                if (nc < chunks) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * ((nc - cbeg) & (kLinInRing - 1)) + q) * kLinInThreads, xr[q] + 4 * nc);
+                }
+                cp_async_commit();
+                cp_async_wait<kLinInRing - 1>();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) v[0][q] = ring[(4 * ((c - cbeg) & (kLinInRing - 1)) + q) * kLinInThreads];
+            }
             // PRECISE: x.w ~ xb.wb (TF32 x TF32, exact products) + xs.wb + xb.ws with the two correction products on
             // bf16 operands (k = 16 per MMA: 4 MMAs per 16 columns instead of 6).  xb is x as the tensor core sees it
             // (low 13 mantissa bits ignored), xs = x - xb exactly; the corrections are 2^-10 of the result, so their
@@ -148,7 +187,7 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float4 a = v[u][q];
-                if (c + PF < chunks) v[u][q] = __ldg(xr[q] + 4 * (c + PF));
+                if constexpr (!RING) { if (c + PF < chunks) v[u][q] = __ldg(xr[q] + 4 * (c + PF)); }
                 if constexpr (PRECISE) {
                     const float e[4] = {a.x, a.y, a.z, a.w};
                     float sm[4];
@@ -200,16 +239,44 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
             }
         }
     }
+    if (!RING || ksplit == 1) {
 #pragma unroll
     for (int m = 0; m < 2; ++m)
 #pragma unroll
         for (int j = 0; j < NT; ++j) {
             const int d = 8 * j + 2 * t;
             const float b0 = bias ? __ldg(bias + d) : 0.f, b1 = bias ? __ldg(bias + d + 1) : 0.f;
-            const int64_t ra = r0 + 16 * m, rb = ra + 8;
+            const int64_t ra = r0 + 16 * m, rbb = ra + 8;
             if (ra < N) store2(y + ra * D + d, acc[m][j][0] + b0, acc[m][j][1] + b1);
-            if (rb < N) store2(y + rb * D + d, acc[m][j][2] + b0, acc[m][j][3] + b1);
+            if (rbb < N) store2(y + rbb * D + d, acc[m][j][2] + b0, acc[m][j][3] + b1);
         }
+    if constexpr (RING) cp_async_wait<0>();
+    } else {
+        // column slices meet in shared memory (the ring's space: every thread's copies have landed and been read)
+        cp_async_wait<0>();
+        __syncthreads();
+        float* part = s_w + D * cs;   // [ksplit][rpc][D]
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int j = 0; j < NT; ++j) {
+                float* pr = part + (static_cast<size_t>(sl) * rpc + rb * 32 + g + 16 * m) * D + 8 * j + 2 * t;
+                *reinterpret_cast<float2*>(pr) = make_float2(acc[m][j][0], acc[m][j][1]);
+                *reinterpret_cast<float2*>(pr + 8 * D) = make_float2(acc[m][j][2], acc[m][j][3]);
+            }
+        __syncthreads();
+        for (int i = threadIdx.x * 2; i < rpc * D; i += kLinInThreads * 2) {   // two consecutive outputs of one row (D is even)
+            const int r = i / D, d = i - r * D;
+            float s0 = 0.f, s1 = 0.f;
+            for (int k = 0; k < ksplit; ++k) {
+                const float2 pv = *reinterpret_cast<const float2*>(part + static_cast<size_t>(k) * rpc * D + i);
+                s0 += pv.x; s1 += pv.y;
+            }
+            const int64_t row = tile * rpc + r;
+            if (row < N) store2(y + row * D + d, s0 + (bias ? __ldg(bias + d) : 0.f), s1 + (bias ? __ldg(bias + d + 1) : 0.f));
+        }
+        __syncthreads();   // the next tile's copies reuse the space
+    }
     }   // tile
 }
 
