@@ -113,24 +113,27 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
     // ksplit ways; the partial sums meet in shared memory and are added in a fixed order (deterministic).  A warp's time
     // is one pass over its columns whatever N is, so without the split 8 192 tokens keep 16 SMs busy for as long as
     // 65 536 keep 128.
+    // the launch may use fewer than kLinInThreads threads (whole warps): a CTA tile is blockDim.x rows, so that the
+    // number of tiles matches the number of SMs (65 536 tokens: 147 tiles of 448 rows instead of 128 of 512)
+    const int nthr = static_cast<int>(blockDim.x);
     constexpr int NT = D / 8;
     extern __shared__ float s_w[];  // [D][C + 16]
     const int cs = C + 16;
     if (w_is_cd) {   // w given as [C][D] (out_linear.weight, for grad_a = grad_y W_out): transpose while staging
-        for (int i = threadIdx.x; i < C * D; i += kLinInThreads) {
+        for (int i = threadIdx.x; i < C * D; i += nthr) {
             const int c = i / D, d = i - c * D;
             s_w[d * cs + c] = __ldg(w + i);
         }
     } else {
-        for (int i = threadIdx.x; i < D * (C / 4); i += kLinInThreads) {
+        for (int i = threadIdx.x; i < D * (C / 4); i += nthr) {
             const int d = i / (C / 4), c4 = i - d * (C / 4);
             *reinterpret_cast<float4*>(&s_w[d * cs + 4 * c4]) = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(d) * C) + c4);
         }
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int rpc = kLinInRows / ksplit;                       // rows per CTA tile
-    const int nrb = (kLinInThreads / 32) / ksplit;             // 32-row blocks per CTA tile
+    const int rpc = nthr / ksplit;                       // rows per CTA tile
+    const int nrb = (nthr / 32) / ksplit;             // 32-row blocks per CTA tile
     const int rb = warp % nrb, sl = warp / nrb;                // this warp: row block, column slice
     for (int64_t tile = blockIdx.x; tile * rpc < N; tile += gridDim.x) {   // persistent: w is staged once per CTA
     const int64_t r0 = tile * rpc + rb * 32 + g;   // rows r0 + 8q, q = 0..3
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
         for (int u = 0; u < kLinInRing - 1; ++u) {
             if (cbeg + u < chunks) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * u + q) * kLinInThreads, xr[q] + 4 * (cbeg + u));
+                for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * u + q) * nthr, xr[q] + 4 * (cbeg + u));
             }
             cp_async_commit();
         }
@@ -171,12 +174,12 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
                 const int nc = c + kLinInRing - 1;
                 if (nc < chunks) {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * ((nc - cbeg) & (kLinInRing - 1)) + q) * kLinInThreads, xr[q] + 4 * nc);
+                    for (int q = 0; q < 4; ++q) cp_async16(ring + (4 * ((nc - cbeg) & (kLinInRing - 1)) + q) * nthr, xr[q] + 4 * nc);
                 }
                 cp_async_commit();
                 cp_async_wait<kLinInRing - 1>();
 #pragma unroll
-                for (int q = 0; q < 4; ++q) v[0][q] = ring[(4 * ((c - cbeg) & (kLinInRing - 1)) + q) * kLinInThreads];
+                for (int q = 0; q < 4; ++q) v[0][q] = ring[(4 * ((c - cbeg) & (kLinInRing - 1)) + q) * nthr];
             }
             // PRECISE: x.w ~ xb.wb (TF32 x TF32, exact products) + xs.wb + xb.ws with the two correction products on
             // bf16 operands (k = 16 per MMA: 4 MMAs per 16 columns instead of 6).  xb is x as the tensor core sees it
@@ -265,7 +268,7 @@ __global__ void __launch_bounds__(kLinInThreads, 1) linear_in_kernel(const float
                 *reinterpret_cast<float2*>(pr + 8 * D) = make_float2(acc[m][j][2], acc[m][j][3]);
             }
         __syncthreads();
-        for (int i = threadIdx.x * 2; i < rpc * D; i += kLinInThreads * 2) {   // two consecutive outputs of one row (D is even)
+        for (int i = threadIdx.x * 2; i < rpc * D; i += nthr * 2) {   // two consecutive outputs of one row (D is even)
             const int r = i / D, d = i - r * D;
             float s0 = 0.f, s1 = 0.f;
             for (int k = 0; k < ksplit; ++k) {
