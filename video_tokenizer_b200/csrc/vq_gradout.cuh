@@ -96,6 +96,8 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const GT* __res
     float acc[NS][NT][4];     // grad_w: (column 256 s + 16 warp + gq [+8], d 8 j + 2 t [+1])
     float cs[NS][2];          // grad_b partial sums of columns 16 warp + gq, + 8 over this lane's tokens
     float gacc[NT][4];        // grad_a of the current tile over this warp's 32 columns of every stage
+    constexpr bool AREG = NS * NT <= 9;   // room in the register file (C = 768, D = 24 yes; C = 1024, D = 32 no)
+    uint32_t afrag[AREG ? kGoTok / 8 : 1][NT][2];   // tf32 B fragments of the current tile's `a` rows
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
         cs[s][0] = cs[s][1] = 0.f;
@@ -158,6 +160,16 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const GT* __res
                 }
                 __syncthreads();
             }
+            if (AREG && s == 0) {
+                // B fragments of grad_w (the tile's `a` rows): the same for every stage of the tile, kept in registers
+#pragma unroll
+                for (int ks = 0; ks < kGoTok / 8; ++ks)
+#pragma unroll
+                    for (int n = 0; n < NT; ++n) {
+                        afrag[ks][n][0] = __float_as_uint(ta[(8 * ks + t) * YS + 8 * n + gq]);
+                        afrag[ks][n][1] = __float_as_uint(ta[(8 * ks + t + 4) * YS + 8 * n + gq]);
+                    }
+            }
             const GT* tile = s_ring + slot * (kGoTok * kGoCols);
             slot = slot == kGoRing - 1 ? 0 : slot + 1;
             // ---- grad_w / grad_b: rows = columns 16 warp + gq (+8), k = tokens
@@ -173,9 +185,13 @@ __global__ void __launch_bounds__(kGoThreads, 1) grad_out_kernel(const GT* __res
                 const uint32_t a0 = tf32_op(x0), a1 = tf32_op(x1), a2 = tf32_op(x2), a3 = tf32_op(x3);
 #pragma unroll
                 for (int n = 0; n < NT; ++n) {
-                    const uint32_t b0 = __float_as_uint(ta[(8 * ks + t) * YS + 8 * n + gq]);
-                    const uint32_t b1 = __float_as_uint(ta[(8 * ks + t + 4) * YS + 8 * n + gq]);
-                    mma_tf32(acc[s][n], a0, a1, a2, a3, b0, b1);
+                    if constexpr (AREG) {
+                        mma_tf32(acc[s][n], a0, a1, a2, a3, afrag[ks][n][0], afrag[ks][n][1]);
+                    } else {
+                        const uint32_t b0 = __float_as_uint(ta[(8 * ks + t) * YS + 8 * n + gq]);
+                        const uint32_t b1 = __float_as_uint(ta[(8 * ks + t + 4) * YS + 8 * n + gq]);
+                        mma_tf32(acc[s][n], a0, a1, a2, a3, b0, b1);
+                    }
                 }
             }
             if constexpr (!WITH_GA) continue;
