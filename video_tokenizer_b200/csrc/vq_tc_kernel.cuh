@@ -84,7 +84,7 @@ struct TcParams {
     int64_t N;
     const uint4* image;       // split-bf16 codebook image (prepare_codebook_tc_kernel)
     int64_t K;                // codes in the image
-    int64_t k_offset;         // global index of code 0 (multiple of 128)
+    int64_t k_offset;         // global index of code 0 (multiple of 256: whole tiles)
     int tiles_per_split;
     int l2norm;
     float t_inv;
@@ -110,7 +110,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 
 // =======================================================================================
-// grid = (row tiles of 128, code splits); block = 576 threads; dynamic smem = tc_smem_bytes<D>()
+// grid = (row tiles of 128, code splits); block = kTcThreads (608: 16 epilogue warps + producer + 2 MMA issuers); dynamic smem = tc_smem_bytes<D>()
 // =======================================================================================
 template <int D>
 __host__ __device__ constexpr size_t tc_smem_bytes() {
