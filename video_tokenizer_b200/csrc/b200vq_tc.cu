@@ -80,11 +80,30 @@ int launch_tc_sample(const void* z, int z_dtype, int64_t z_row_stride, int64_t N
     ts.keys = reinterpret_cast<unsigned long long*>(keys); ts.n_events = n_events;
     ts.debug = env_int("B200VQ_TC_DEBUG", 0);
     // warm start: scan the first eighth of the CTA's tiles for the row's best code before testing
-    ts.scout_tiles = std::min(per, std::max(0, env_int("B200VQ_TS_SCOUT", per >= 16 ? per / 8 : (per >= 8 ? 1 : 0))));
+    auto scout_for = [](int tiles) { return std::min(tiles, std::max(0, env_int("B200VQ_TS_SCOUT", tiles >= 16 ? tiles / 8 : (tiles >= 8 ? 1 : 0)))); };
+    ts.scout_tiles = scout_for(per);
+    ts.head_row_tiles = static_cast<int>(row_tiles); ts.splits = splits;
+    ts.tail_splits = 1; ts.tail_tiles_per_split = per; ts.tail_scout_tiles = ts.scout_tiles;
+    // Large batches: row_tiles / SMs waves of one CTA per SM, the last one partly filled (65 536 rows: 3.46 -> the
+    // fourth wave runs 68 CTAs on 148 SMs).  Its row tiles are split over the codes so that it takes 1 / tail_splits
+    // of a wave (keys of the parts merge through atomicMax like any other code split).
+    const int sms = sm_count();
+    const int64_t rem = row_tiles % sms;
+    if (splits == 1 && row_tiles > sms && rem > 0 && env_int("B200VQ_TS_TAIL", 1) != 0) {
+        int tsp = static_cast<int>(std::min<int64_t>(4, sms / rem));
+        while (tsp > 1 && total_tiles / tsp < 8) --tsp;
+        if (const int forced = env_int("B200VQ_TS_TAIL_SPLITS", 0)) tsp = std::max(1, std::min(forced, total_tiles));
+        if (tsp > 1) {
+            ts.head_row_tiles = static_cast<int>(row_tiles - rem);
+            ts.tail_splits = tsp;
+            ts.tail_tiles_per_split = (total_tiles + tsp - 1) / tsp;
+            ts.tail_scout_tiles = scout_for(ts.tail_tiles_per_split);
+        }
+    }
     ts.flush_early = std::max(1, env_int("B200VQ_TS_FLUSH_EARLY", 8));
     ts.flush_late = std::max(1, env_int("B200VQ_TS_FLUSH_LATE", 32));
     ts.early_iters = env_int("B200VQ_TS_EARLY_ITERS", 2);
-    dim3 grid(static_cast<unsigned>(row_tiles), static_cast<unsigned>(splits));
+    dim3 grid(static_cast<unsigned>(static_cast<int64_t>(ts.head_row_tiles) * splits + (row_tiles - ts.head_row_tiles) * ts.tail_splits));
     int rc = B200VQ_OK;
     B200VQ_DISPATCH_DTYPE(z_dtype, T, {
         switch (D) {

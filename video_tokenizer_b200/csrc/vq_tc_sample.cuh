@@ -65,6 +65,11 @@ struct TsParams {
     int64_t k_offset;         // global index of code 0 (multiple of 256)
     int tiles_per_split;
     int scout_tiles;          // tiles scanned for a warm-start group before testing (0 = none)
+    // 1-D grid.  The first head_row_tiles row tiles are split `splits` ways over the codes (tiles_per_split each); the
+    // remaining row tiles -- the last, partly filled wave of a large batch -- are split tail_splits ways
+    // (tail_tiles_per_split each, tail_scout_tiles) so that the wave is short instead of mostly empty.
+    int head_row_tiles, splits;
+    int tail_splits, tail_tiles_per_split, tail_scout_tiles;
     int l2norm;
     float t_inv;
     uint64_t seed, offset;
@@ -195,11 +200,17 @@ __global__ void __launch_bounds__(kTsThreads, 1) tc_sample_kernel(const TsParams
     uint32_t* s_qtail = s_tmem + 4;   // (kTcEpiWarps) queue tails
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t row0 = static_cast<int64_t>(blockIdx.x) * kTcRows;
     const int total_tiles = static_cast<int>((p.K + kTcCodes - 1) / kTcCodes);
-    const int tile_begin = blockIdx.y * p.tiles_per_split;
-    const int ntiles = min(p.tiles_per_split, total_tiles - tile_begin);
-    const int scout = min(p.scout_tiles, ntiles);
+    const int head_ctas = p.head_row_tiles * p.splits;
+    const bool tail = static_cast<int>(blockIdx.x) >= head_ctas;
+    const int tb = static_cast<int>(blockIdx.x) - head_ctas;
+    const int row_tile = tail ? p.head_row_tiles + tb / p.tail_splits : static_cast<int>(blockIdx.x) % p.head_row_tiles;
+    const int part = tail ? tb % p.tail_splits : static_cast<int>(blockIdx.x) / p.head_row_tiles;
+    const int per = tail ? p.tail_tiles_per_split : p.tiles_per_split;
+    const int64_t row0 = static_cast<int64_t>(row_tile) * kTcRows;
+    const int tile_begin = part * per;
+    const int ntiles = max(0, min(per, total_tiles - tile_begin));
+    const int scout = min(tail ? p.tail_scout_tiles : p.scout_tiles, ntiles);
     const int iters = ntiles + scout;           // iteration j: tile j (scan only while j < scout), then tiles 0..scout-1 again
     const uint32_t first_code = static_cast<uint32_t>(p.k_offset) + tile_begin * kTcCodes;
     const uint64_t seed = p.philox_dev ? p.philox_dev[0] : p.seed, offset = p.philox_dev ? p.philox_dev[1] : p.offset;
