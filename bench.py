@@ -456,6 +456,11 @@ def codebook_sharded_leg(V, dev, world, rank):
     return rec
 
 
+def _trace(msg):
+    if os.environ.get("B200VQ_BENCH_TRACE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')}] {msg}", file=sys.stderr, flush=True)
+
+
 def run_b200(args):
     import torch.distributed as dist
 
@@ -523,24 +528,50 @@ def run_b200(args):
     ms_step, value_kind = ms_eager, "eager module call"
     if args.mode == "stochastic" and os.environ.get("B200VQ_BENCH_NO_GRAPH") is None:
         try:
-            graphed = V.GraphedBottleneckStep(m, x.detach(), G, loss_q_grad=CFG["loss_q_weight"], warmup=2)
+            sync_in_graph = False
+            if world > 1 and os.environ.get("B200VQ_BENCH_SYNC_IN_GRAPH") is not None:   # opt-in
+                # the whole data-parallel step in the graph: the all-reduce is captured too and starts behind the
+                # backward's grads-ready event, beside the grad_x pass
+                try:
+                    sharded.enable_grad_overlap(dev)
+                    graphed = V.GraphedBottleneckStep(m, x.detach(), G, loss_q_grad=CFG["loss_q_weight"], warmup=2,
+                                                      post_backward=lambda: sharded.token_sharded_sync(m))
+                    sync_in_graph = True
+                except Exception as e:   # pragma: no cover
+                    sharded.disable_grad_overlap(dev)
+                    print(f"bench.py: rank {rank}: captured sync unavailable ({type(e).__name__}: {e}); syncing after the replay",
+                          file=sys.stderr)
+                    graphed = None
+            if graphed is None:
+                graphed = V.GraphedBottleneckStep(m, x.detach(), G, loss_q_grad=CFG["loss_q_weight"], warmup=2)
+
+            _trace(f"graph captured (sync_in_graph={sync_in_graph})")
 
             def gstep():
                 graphed.replay()
-                if world > 1:
+                if world > 1 and not sync_in_graph:
                     sharded.token_sharded_sync(m)
 
             for _ in range(warm):
                 gstep()
+            _trace("graph warm-up enqueued")
             barrier()
+            _trace("graph warm-up done")
             ms_step = max_over_ranks(time_events(gstep, args.steps, sampler, barrier))
+            _trace("graph timed")
             value_kind = "CUDA-graph replay of the module's fwd+bwd (GraphedBottleneckStep)"
+            if world > 1:
+                value_kind += (" with the gradient / histogram all-reduce captured in the graph behind the grads-ready event"
+                               if sync_in_graph else " followed by the gradient / histogram all-reduce")
         except Exception as e:   # pragma: no cover -- keep the eager number rather than no number
             graphed = None
             value_kind = f"eager module call (graph capture failed: {type(e).__name__}: {e})"[:200]
         m.regularizer.disable_device_rng()
+        if world > 1:
+            sharded.disable_grad_overlap(dev)   # the eager legs below sync in stream order
     value = world * N / (ms_step * 1e-3)
 
+    _trace("device-resident legs done")
     # ---- end to end through the public module API with HOST buffers ---------------------------
     xh = torch.randn(B, n, C).pin_memory()
     gh = torch.randn(B, n, C).pin_memory()

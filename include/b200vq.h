@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VQ_VERSION 121
+#define B200VQ_VERSION 122
 
 /* element types of z / grad_z */
 #define B200VQ_DT_F32 0
@@ -347,7 +347,13 @@ int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, co
                                const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,
                                const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
                                int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
-                               float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream);
+                               float* grad_b_out, void* workspace, size_t workspace_bytes, void* grads_ready_event,
+                               b200vq_stream_t stream);
+
+/* grads_ready_event (cudaEvent_t, nullable): recorded once every PARAMETER gradient (grad_w_in, grad_b_in,
+ * grad_weight, grad_w_out, grad_b_out) has been enqueued and BEFORE the grad_x pass, so that a data-parallel caller can
+ * start its gradient all-reduce on another stream while grad_x (one pass of stores over (N, C)) is still being written
+ * (the reference's DDP overlaps bucket all-reduces with backward the same way, trainers/base_trainer.py:388). */
 
 /* out3 = {*a, *b, *c} with 0 for null pointers: packs the upstream gradients of loss_q / loss_commit /
  * loss_codebook (three separate 0-dim tensors under autograd) into the g_losses vector of the backward calls. */

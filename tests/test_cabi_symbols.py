@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_host_only_entry_points():
     lib = _lib.load()
-    assert lib.b200vq_version() == 121
+    assert lib.b200vq_version() == 122
     assert lib.b200vq_max_dim() == 1024
     assert lib.b200vq_error_string(0) == b"ok"
     assert lib.b200vq_error_string(-2) == b"unsupported code dimension"

@@ -107,11 +107,30 @@ def _token_sharded(rank, world):
     usage = sharded.token_sharded_sync(m)
     torch.cuda.synchronize()
     gerr = max(float((p.grad - r).abs().max() / (r.abs().max() + 1e-20)) for p, r in zip(m.parameters(), ref_g))
-    return dict(gerr=gerr, hist_equal=all(bool(torch.equal(a, b)) for a, b in zip(usage, ref_h)),
-                fast_path=sharded._flat_of([p.grad for p in m.parameters()])[0] is not None)
+    res = dict(gerr=gerr, hist_equal=all(bool(torch.equal(a, b)) for a, b in zip(usage, ref_h)),
+               fast_path=sharded._flat_of([p.grad for p in m.parameters()])[0] is not None)
+    # the same sync started behind the backward's grads-ready event on its own stream (beside the grad_x pass),
+    # eager and captured in a CUDA graph together with the step
+    sharded.enable_grad_overlap(dev)
+    run(xs[rank], Gs[rank])
+    usage = sharded.token_sharded_sync(m)
+    torch.cuda.synchronize()
+    res["gerr_overlap"] = max(float((p.grad - r).abs().max() / (r.abs().max() + 1e-20)) for p, r in zip(m.parameters(), ref_g))
+    res["hist_equal_overlap"] = all(bool(torch.equal(a, b)) for a, b in zip(usage, ref_h))
+    step = V.GraphedBottleneckStep(m, xs[rank].to(dev), Gs[rank].to(dev), loss_q_grad=0.1, warmup=2,
+                                   post_backward=lambda: sharded.token_sharded_sync(m))
+    for _ in range(2):
+        step.replay()
+    torch.cuda.synchronize()
+    res["gerr_graph"] = max(float((p.grad - r).abs().max() / (r.abs().max() + 1e-20)) for p, r in zip(m.parameters(), ref_g))
+    res["hist_equal_graph"] = all(bool(torch.equal(a, b)) for a, b in zip(m.regularizer.last_usage, ref_h))
+    sharded.disable_grad_overlap(dev)
+    return res
 
 
 def test_token_sharded_sync_two_gpus():
     out = _run("_token_sharded")
     for rank in (0, 1):
         assert out[rank]["gerr"] < 1e-5 and out[rank]["hist_equal"] and out[rank]["fast_path"], out[rank]
+        assert out[rank]["gerr_overlap"] < 1e-5 and out[rank]["hist_equal_overlap"], out[rank]
+        assert out[rank]["gerr_graph"] < 1e-5 and out[rank]["hist_equal_graph"], out[rank]

@@ -68,7 +68,7 @@ SIGNATURES = {
     "b200vq_bottleneck_forward": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _f32,
                                          _u64, _u64, _i64, _f32, _f32, _i32] + [_vp] * 13 + [_i64, _vp, _sz, _vp, _i32, _vp, _i64, _vp]),
     "b200vq_bottleneck_backward": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32] + [_vp] * 8
-                                   + [_i64, _i32, _i32, _f32, _f32, _vp, _i64] + [_vp] * 6 + [_sz, _vp]),
+                                   + [_i64, _i32, _i32, _f32, _f32, _vp, _i64] + [_vp] * 6 + [_sz, _vp, _vp]),
 }
 
 
@@ -102,7 +102,7 @@ def load(build_if_missing: bool = True):
             except AttributeError as e:
                 raise B200VQError(f"{path} does not export {name}") from e
             fn.restype, fn.argtypes = res, args
-        if lib.b200vq_version() < 121:
+        if lib.b200vq_version() < 122:
             raise B200VQError("libb200vq.so is older than this Python package")
         _lib = lib
         return lib

@@ -503,7 +503,8 @@ int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, co
                                const float* wnorm, const float* znorm, const float* zlen, const int64_t* idx,
                                const float* ste, int64_t K, int D, int l2norm, float beta, float w_cb, float* grad_x,
                                int64_t ldgx, float* grad_w_in, float* grad_b_in, float* grad_weight, float* grad_w_out,
-                               float* grad_b_out, void* workspace, size_t workspace_bytes, b200vq_stream_t stream) {
+                               float* grad_b_out, void* workspace, size_t workspace_bytes, void* grads_ready_event,
+                               b200vq_stream_t stream) {
     if (N <= 0 || K <= 0 || !valid_dtype(act_dtype)) return B200VQ_EINVAL;
     if (!b200vq_linear_supported(C, D)) return B200VQ_EDIM;
     if (!x || !w_in || !w_out || !emb || !wnorm || !znorm || !zlen || !idx || !ste) return B200VQ_EINVAL;
@@ -548,7 +549,11 @@ int b200vq_bottleneck_backward(const void* g_out, int act_dtype, int64_t ldg, co
     cudaStream_t s2 = sc.side();
     if (grad_weight && (rc = b200vq_codebook_backward(gemb, g_emb, emb, wnorm, K, D, l2norm, grad_weight, s2))) return rc;
     if (grad_b_in && (rc = b200vq_colsum(gz, N, D, grad_b_in, s2))) return rc;
-    if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, (forks & 8) ? st : s2))) return rc;
+    // with a ready-event every parameter gradient goes to the lane (or stays on the caller's stream when there is none),
+    // so that ONE record covers them all
+    cudaStream_t wg_stream = (forks & 8) && !grads_ready_event ? st : s2;
+    if (grad_w_in && (rc = launch_weight_grad(x, ldx, gz, N, C, D, grad_w_in, 1, nullptr, wgp, wg_stream))) return rc;
+    if (grads_ready_event && (rc = cuda_check(cudaEventRecord(static_cast<cudaEvent_t>(grads_ready_event), s2)))) return rc;
     if (grad_x && (rc = b200vq_linear_out(gz, N, D, w_in, 1, nullptr, C, grad_x, ldgx, stream))) return rc;
     return sc.join();
 }

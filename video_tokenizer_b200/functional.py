@@ -15,6 +15,9 @@ from . import _lib
 
 _DTYPES = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16, torch.float16: _lib.DT_F16}
 _workspaces: dict = {}
+# device index -> torch.cuda.Event the one-call backward records when its parameter gradients are enqueued
+# (sharded.enable_grad_overlap); absent = no event
+GRADS_READY: dict = {}
 
 # "tc": tcgen05 tensor-core scoring where supported (default); "exact": fp32 CUDA-core scoring.
 # Deterministic indices are identical either way (tests/test_gpu_tc.py).
@@ -618,11 +621,14 @@ class _BottleneckFunction(torch.autograd.Function):
                 g_losses = torch.empty(3, **f32)
                 _lib.check(lib.b200vq_pack3(_ptr(g_lq), _ptr(g_lc), _ptr(g_lcb), g_losses.data_ptr(), _stream()), "b200vq_pack3")
             ws = _workspace(dev, lib.b200vq_bottleneck_workspace_bytes(N, C, D, K))
+            # data-parallel jobs: an event recorded when the parameter gradients are enqueued, before the grad_x pass
+            # (sharded.token_sharded_sync starts its all-reduce behind it on another stream)
+            ready = GRADS_READY.get(dev.index) if sync else None
             rc = lib.b200vq_bottleneck_backward(
                 _ptr(go), _DTYPES[act_dtype], ldg, _ptr(g_losses), _ptr(g_ste), _ptr(g_znorm), _ptr(g_emb), _ptr(g_z), xx.data_ptr(), ldx, N, C,
                 w_in.data_ptr(), w_out.data_ptr(), emb.data_ptr(), wnorm.data_ptr(), znorm.data_ptr(), zlen.data_ptr(),
                 idx.data_ptr(), ste.data_ptr(), K, D, int(l2norm), beta, w_cb, _ptr(gx), C, _ptr(gw_in), _ptr(gb_in), _ptr(gw),
-                _ptr(gw_out), _ptr(gb_out), ws.data_ptr(), ws.numel(), _stream())
+                _ptr(gw_out), _ptr(gb_out), ws.data_ptr(), ws.numel(), ready.cuda_event if ready is not None else None, _stream())
             _lib.check(rc, "b200vq_bottleneck_backward")
         return gx, gw_in, gb_in, gw, gw_out, gb_out, None
 

@@ -24,11 +24,14 @@ class GraphedBottleneckStep:
     parameters' `.grad` (overwritten, not accumulated, on every replay)."""
 
     def __init__(self, module, x: torch.Tensor, grad_output: torch.Tensor, loss_q_grad: float = 0.1, warmup: int = 3,
-                 autocast_dtype: Optional[torch.dtype] = None):
+                 autocast_dtype: Optional[torch.dtype] = None, post_backward=None):
         if not x.is_cuda:
             raise RuntimeError("GraphedBottleneckStep needs CUDA tensors")
         self.module = module
         self.autocast_dtype = autocast_dtype   # bf16 / fp16: the step runs inside torch.autocast (grad_output in that dtype)
+        # optional callable run right after backward INSIDE the captured step, e.g. the data-parallel gradient sync
+        # (sharded.token_sharded_sync: NCCL collectives are capturable), so that a replay is the whole training step
+        self.post_backward = post_backward
         self.reg = module.regularizer
         self.x = x.detach().clone().requires_grad_(True)
         self.g = grad_output.detach().clone()
@@ -58,6 +61,8 @@ class GraphedBottleneckStep:
             out = self.module(self.x)
         stats = self.reg.code_usage() if hasattr(self.reg, "code_usage") else None
         torch.autograd.backward([out["output"], out["loss_q"]], [self.g, self.gq])
+        if self.post_backward is not None:
+            self.post_backward()
         return out, stats
 
     def sync_rng(self):

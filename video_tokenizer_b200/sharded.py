@@ -97,6 +97,40 @@ def _flat_of(grads: Sequence[torch.Tensor]):
     return None, 0, None, 1
 
 
+_SYNC_STREAMS: dict = {}
+
+
+def enable_grad_overlap(device=None) -> None:
+    """Let `token_sharded_sync` start its all-reduce while the backward's grad_x pass is still running: the one-call
+    backward then records an event once the parameter gradients are enqueued (b200vq_bottleneck_backward,
+    `grads_ready_event`), and the sync waits for that event on a stream of its own instead of for the whole backward.
+    Call once per process after torch.cuda.set_device; `disable_grad_overlap()` goes back to the in-order sync."""
+    from . import functional as VF
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ev = torch.cuda.Event()
+    with torch.cuda.device(dev):
+        ev.record()          # creates the underlying cudaEvent_t (torch makes it lazily)
+    VF.GRADS_READY[dev.index] = ev
+    _SYNC_STREAMS.setdefault(dev.index, torch.cuda.Stream(device=dev))
+
+
+def disable_grad_overlap(device=None) -> None:
+    from . import functional as VF
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    VF.GRADS_READY.pop(dev.index, None)
+
+
+def _ready_event(flat: torch.Tensor):
+    if not flat.is_cuda:
+        return None
+    from . import functional as VF
+    return VF.GRADS_READY.get(flat.device.index)
+
+
+def _sync_stream(device) -> "torch.cuda.Stream":
+    return _SYNC_STREAMS[device.index]
+
+
 def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
     """After loss.backward() on every rank: average the bottleneck's parameter grads and sum
     the fused usage histograms across ranks in ONE collective.  Returns the global
@@ -114,6 +148,17 @@ def token_sharded_sync(bottleneck, group=None) -> Optional[Tuple[torch.Tensor, t
             tail_ok = hists is not None and usage is not None and _same_storage(usage[0], hists)
             if tail_ok and scale == world:
                 # histograms were pre-multiplied by the world size: AVG gives mean gradients and summed counts
+                ready = _ready_event(flat)
+                if ready is not None:
+                    # the one-call backward recorded `ready` when the parameter gradients were enqueued and went on to
+                    # write grad_x: the collective runs beside that pass on its own stream
+                    cur, side = torch.cuda.current_stream(flat.device), _sync_stream(flat.device)
+                    side.wait_event(ready)
+                    with torch.cuda.stream(side):
+                        dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)
+                        hists.view(-1).copy_(flat[tot:])
+                    cur.wait_stream(side)
+                    return usage
                 dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)
                 hists.view(-1).copy_(flat[tot:])
                 return usage
