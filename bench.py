@@ -636,6 +636,8 @@ def run_b200(args):
 
     if rank != 0:
         if world > 1:
+            graphed = None            # a graph that holds a captured collective goes before its communicator
+            torch.cuda.synchronize()
             dist.barrier()
             dist.destroy_process_group()
         return
@@ -763,6 +765,8 @@ def run_b200(args):
     }
     print(json.dumps(line), flush=True)
     if world > 1:
+        graphed = None            # a graph that holds a captured collective goes before its communicator
+        torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
 
