@@ -1,5 +1,7 @@
 // b200vq -- C ABI (include/b200vq.h) over the sm_100a kernels.  No torch types here.
 // This unit: the tcgen05 tensor-core scoring path.
+#include <type_traits>
+
 #include "vq_tc_sample.cuh"
 #include "b200vq_host.h"
 
@@ -17,6 +19,13 @@ int launch_tc(const TcParams& prm, dim3 grid, cudaStream_t st) {
 template <int DD, typename T>
 int launch_ts(const TsParams& prm, dim3 grid, cudaStream_t st) {
     constexpr size_t smem = ts_smem_bytes<DD>();
+    if constexpr (DD == 24 && std::is_same<T, float>::value) {
+        if (prm.debug != 0) {   // tuning switches exist in this one instantiation only
+            if (int rc = set_smem(tc_sample_kernel<DD, T, true>, smem)) return rc;
+            tc_sample_kernel<DD, T, true><<<grid, kTsThreads, smem, st>>>(prm);
+            return launch_check();
+        }
+    }
     if (int rc = set_smem(tc_sample_kernel<DD, T>, smem)) return rc;
     tc_sample_kernel<DD, T><<<grid, kTsThreads, smem, st>>>(prm);
     return launch_check();
