@@ -567,7 +567,7 @@ def run_b200(args):
             graphed = None
             value_kind = f"eager module call (graph capture failed: {type(e).__name__}: {e})"[:200]
         m.regularizer.disable_device_rng()
-        if world > 1:
+        if world > 1 and os.environ.get("B200VQ_BENCH_KEEP_OVERLAP") is None:
             sharded.disable_grad_overlap(dev)   # the eager legs below sync in stream order
     value = world * N / (ms_step * 1e-3)
 
@@ -600,13 +600,16 @@ def run_b200(args):
             state["primed"] = True
         issue_copies(cur ^ 1)                            # prefetch the next step's inputs
         torch.cuda.current_stream().wait_event(ready[cur])
+        _trace(f"e2e step {state['i']}: inputs ready")
         out, stats = step(xd[cur], gd[cur])
+        _trace(f"e2e step {state['i']}: step enqueued")
         consumed[cur].record()
         idx_h.copy_(out["bottleneck_rep"], non_blocking=True)
         sc_h[:3].copy_(torch.stack([out["loss_q"].detach(), out["loss_commit"].detach(), out["loss_codebook"].detach()]),
                        non_blocking=True)
         sc_h[3:7].copy_(stats, non_blocking=True)
         torch.cuda.synchronize()  # the caller reads the step's result on the host
+        _trace(f"e2e step {state['i']}: synchronized")
         state["i"] += 1
         return float(sc_h[0])
 
