@@ -65,6 +65,12 @@ class GraphedBottleneckStep:
             self.post_backward()
         return out, stats
 
+    def release(self):
+        """Drop the captured graph (and its memory pool).  Call before torch.distributed.destroy_process_group() when
+        `post_backward` captured a collective: a live graph that holds one keeps the communicator busy at teardown."""
+        self.graph = None
+        self.out = self.stats = None
+
     def sync_rng(self):
         """take (seed, offset) from the torch CUDA generator again (e.g. after torch.cuda.manual_seed)"""
         self.reg.enable_device_rng(self.x.device)
