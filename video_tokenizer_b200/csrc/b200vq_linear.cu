@@ -94,6 +94,37 @@ int launch_linear_out(const float* a, int64_t N, int D, const float* w, int w_is
     if ((ldy & 3) || (reinterpret_cast<uintptr_t>(y) & (y_dtype == B200VQ_DT_F32 ? 15 : 7)) || (reinterpret_cast<uintptr_t>(w) & 15))
         return B200VQ_EALIGN;
     if (add && (add_rows <= 0 || (reinterpret_cast<uintptr_t>(add) & 15))) return add_rows <= 0 ? B200VQ_EINVAL : B200VQ_EALIGN;
+    // column-stationary kernel (weights in registers, no shared memory) whenever 16 warps x 4 groups cover the columns
+    static const bool lo_old = std::getenv("B200VQ_LO_OLD") != nullptr;   // tuning aid: the shared-memory kernel
+    const int ngroups = C / 16, G = (ngroups + kLinOutThreads / 32 - 1) / (kLinOutThreads / 32);
+    if (!gidx && !lo_old && G >= 1 && G <= 4 && !(reinterpret_cast<uintptr_t>(a) & 7)) {
+        const unsigned cblocks = static_cast<unsigned>(std::min<int64_t>((N + 15) / 16, static_cast<int64_t>(sm_count())));
+        int rc2 = B200VQ_OK;
+#define B200VQ_LO_COLS(DD, GG, OT) \
+        linear_out_cols_kernel<DD, GG, OT><<<cblocks, kLinOutThreads, 0, st>>>(a, N, w, w_is_dc, bias, C, static_cast<OT*>(y), ldy, add, add_rows)
+#define B200VQ_LO_COLS_G(DD, OT)                                  \
+        switch (G) {                                              \
+            case 1: B200VQ_LO_COLS(DD, 1, OT); break;             \
+            case 2: B200VQ_LO_COLS(DD, 2, OT); break;             \
+            case 3: B200VQ_LO_COLS(DD, 3, OT); break;             \
+            default: B200VQ_LO_COLS(DD, 4, OT); break;            \
+        }
+#define B200VQ_LO_COLS_T(DD)                                                       \
+        if (y_dtype == B200VQ_DT_F32) { B200VQ_LO_COLS_G(DD, float) }              \
+        else if (y_dtype == B200VQ_DT_BF16) { B200VQ_LO_COLS_G(DD, __nv_bfloat16) } \
+        else { B200VQ_LO_COLS_G(DD, __half) }
+        switch (D) {
+            case 8: B200VQ_LO_COLS_T(8); break;
+            case 16: B200VQ_LO_COLS_T(16); break;
+            case 24: B200VQ_LO_COLS_T(24); break;
+            default: B200VQ_LO_COLS_T(32); break;
+        }
+#undef B200VQ_LO_COLS_T
+#undef B200VQ_LO_COLS_G
+#undef B200VQ_LO_COLS
+        (void)rc2;
+        return launch_check();
+    }
     const size_t smem = static_cast<size_t>(C) * (D + 5) * 4;
     int lo_dbg = 0, lo_grid = 1;   // one 16-warp CTA per SM: the weight staging is paid once per SM
     if (const char* env = std::getenv("B200VQ_LO_DEBUG")) lo_dbg = std::atoi(env);

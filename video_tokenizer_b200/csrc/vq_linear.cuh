@@ -398,6 +398,90 @@ __global__ void __launch_bounds__(kLinOutThreads) linear_out_kernel(const float*
 }
 
 // =======================================================================================
+// linear_out, column-stationary: every warp of the CTA owns G consecutive 16-column groups for the whole kernel and keeps
+// their B fragments (TF32) and bias IN REGISTERS; all 16 warps walk the same 16-row tiles.  Per row tile and group a warp
+// issues 2 * D/8 MMAs and two 16-byte stores and nothing else -- the shared-memory kernel above spends 12 LDS on the same
+// 6 MMAs, and LSU issue is what bounds it (a bf16 output, half the bytes, takes as long as fp32).  No shared memory, no
+// weight staging: a small batch does not pay for it either.  C <= 16 * 16 * G columns, G <= 4.
+// Contraction index permutation: MMA k = t reads d = 8s + 2t and k = t + 4 reads d = 8s + 2t + 1 in BOTH operands, so a
+// lane's A elements of a k8 step are one 8-byte load.
+// =======================================================================================
+template <int D, int G, typename OT>
+__global__ void __launch_bounds__(kLinOutThreads, 1) linear_out_cols_kernel(const float* __restrict__ a, int64_t N,
+                                                                            const float* __restrict__ w, int w_is_dc,
+                                                                            const float* __restrict__ bias, int C,
+                                                                            OT* __restrict__ y, int64_t ldy,
+                                                                            const float* __restrict__ add, int64_t add_rows) {
+    constexpr int KS = D / 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int ngroups = C / 16, j0 = warp * G;
+    // output column (inside a 16-column group) behind MMA column g of the group's first n8 tile; the second tile: + 2
+    // (a lane's two C fragments are then four CONSECUTIVE output columns: one 16-byte store per row)
+    const int wrow = 4 * (g >> 1) + (g & 1);
+    uint32_t wb[G][2][KS][2];
+    float bs[G][4];
+#pragma unroll
+    for (int jj = 0; jj < G; ++jj) {
+        const int j = j0 + jj;
+        const bool valid = j < ngroups;
+#pragma unroll
+        for (int tile = 0; tile < 2; ++tile) {
+            const int col = 16 * j + wrow + 2 * tile;
+#pragma unroll
+            for (int s = 0; s < KS; ++s) {
+                const int d0 = 8 * s + 2 * t;
+                float w0 = 0.f, w1 = 0.f;
+                if (valid) {
+                    w0 = w_is_dc ? __ldg(w + static_cast<int64_t>(d0) * C + col) : __ldg(w + static_cast<int64_t>(col) * D + d0);
+                    w1 = w_is_dc ? __ldg(w + static_cast<int64_t>(d0 + 1) * C + col) : __ldg(w + static_cast<int64_t>(col) * D + d0 + 1);
+                }
+                wb[jj][tile][s][0] = tf32_rna(w0);
+                wb[jj][tile][s][1] = tf32_rna(w1);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) bs[jj][e] = (valid && bias) ? __ldg(bias + 16 * j + 4 * t + e) : 0.f;
+    }
+    const int64_t tiles = (N + 15) / 16;
+    for (int64_t rt = blockIdx.x; rt < tiles; rt += gridDim.x) {
+        const int64_t r0 = rt * 16 + g;
+        const int64_t ra = min(r0, N - 1), rb = min(r0 + 8, N - 1);
+        uint32_t fa[KS][4];
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+            const float2 va = __ldg(reinterpret_cast<const float2*>(a + ra * D + 8 * s + 2 * t));
+            const float2 vb = __ldg(reinterpret_cast<const float2*>(a + rb * D + 8 * s + 2 * t));
+            fa[s][0] = tf32_rna(va.x); fa[s][1] = tf32_rna(vb.x); fa[s][2] = tf32_rna(va.y); fa[s][3] = tf32_rna(vb.y);
+        }
+        const bool oka = r0 < N, okb = r0 + 8 < N;
+        const float* pa = add ? add + (ra % add_rows) * C + 4 * t : nullptr;
+        const float* pb = add ? add + (rb % add_rows) * C + 4 * t : nullptr;
+        OT* ya = y + r0 * ldy + 4 * t;
+        OT* yb = y + (r0 + 8) * ldy + 4 * t;
+#pragma unroll
+        for (int jj = 0; jj < G; ++jj) {
+            const int j = j0 + jj;
+            if (j >= ngroups) break;
+            float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int s = 0; s < KS; ++s) {
+                mma_tf32(acc0, fa[s][0], fa[s][1], fa[s][2], fa[s][3], wb[jj][0][s][0], wb[jj][0][s][1]);
+                mma_tf32(acc1, fa[s][0], fa[s][1], fa[s][2], fa[s][3], wb[jj][1][s][0], wb[jj][1][s][1]);
+            }
+            float oa[4] = {acc0[0] + bs[jj][0], acc0[1] + bs[jj][1], acc1[0] + bs[jj][2], acc1[1] + bs[jj][3]};
+            float ob[4] = {acc0[2] + bs[jj][0], acc0[3] + bs[jj][1], acc1[2] + bs[jj][2], acc1[3] + bs[jj][3]};
+            if (add) {
+                const float4 ea = __ldg(reinterpret_cast<const float4*>(pa + 16 * j)), eb = __ldg(reinterpret_cast<const float4*>(pb + 16 * j));
+                oa[0] += ea.x; oa[1] += ea.y; oa[2] += ea.z; oa[3] += ea.w;
+                ob[0] += eb.x; ob[1] += eb.y; ob[2] += eb.z; ob[3] += eb.w;
+            }
+            if (oka) store4_cs(ya + 16 * j, oa[0], oa[1], oa[2], oa[3]);
+            if (okb) store4_cs(yb + 16 * j, ob[0], ob[1], ob[2], ob[3]);
+        }
+    }
+}
+
+// =======================================================================================
 // weight_grad:  dw[c][d] += sum_n x[n][c] * y[n][d]     colsum[c] += sum_n x[n][c]
 // (x: N x C row stride ldx -- the activation or the upstream gradient; y: N x D.)
 // Used for out_linear.weight.grad (x = grad_output, y = regularized_z; colsum = bias grad)
